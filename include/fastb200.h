@@ -1,0 +1,185 @@
+/*
+ * fastb200.h -- C ABI of the B200-native (sm_100a) FAST hot path.
+ *
+ * Every entry point is what a binding of the reference's hot path would call; the reference symbol each one
+ * replaces is cited as file:line relative to kidusabe1/Imagined-Speech-Decoding.  The library is plain CUDA
+ * (no torch types in any signature): pointers are device pointers unless stated, sizes are element counts,
+ * `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *
+ * Conventions
+ *   - return 0 on success, <0 for an invalid argument / unsupported shape, >0 = cudaError_t of the launch.
+ *     fastb200_last_error() returns a thread-local, human readable message for the last non-zero return.
+ *   - no entry point allocates, frees, retains a pointer past the call, or synchronises the device.
+ *   - all kernels launch on the caller's stream; entry points are re-entrant given disjoint buffers.
+ *   - all floating point tensors are fp32 unless stated; all layouts are dense row-major.
+ */
+#ifndef FASTB200_H
+#define FASTB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FASTB200_MAX_ZONES   16
+#define FASTB200_MAX_CHANS   256
+#define FASTB200_MAX_LAYERS  16
+#define FASTB200_TAPS        5      /* Conv4Layers temporal kernel length (fast.py:106-109) */
+
+/* Forward modes of FAST.forward (src/fast/models/fast.py:270-284). */
+#define FASTB200_MODE_DEFAULT     0
+#define FASTB200_MODE_TRAIN_HEAD  1
+
+/*
+ * Static description of one FAST model: the 12 config attributes FAST.__init__ reads (fast.py:219-230), the
+ * zone gather table Head builds (fast.py:205-206), and the element offsets of every parameter inside ONE flat
+ * fp32 buffer holding the parameters in state_dict order (SURVEY.md section 8b "state_dict wire format").
+ * The host fills it once per model; it is passed by pointer to host memory and copied by value into launches.
+ */
+typedef struct fastb200_model {
+    int32_t n_chan;        /* C   electrodes per trial                           */
+    int32_t window_len;    /* W   config.window_len                              */
+    int32_t slide_step;    /* S   config.slide_step                              */
+    int32_t n_zones;       /* Z   len(zone_dict)            <= FASTB200_MAX_ZONES */
+    int32_t dim_cnn;       /* F   config.dim_cnn            in {8,16,32}          */
+    int32_t dim_token;     /* D   config.dim_token          <= 128, D % heads == 0 */
+    int32_t n_heads;       /* H   config.num_heads                                */
+    int32_t n_layers;      /* L   config.num_layers         <= FASTB200_MAX_LAYERS */
+    int32_t dim_hidden;    /* 2*D AttentionBlock hidden_dim (fast.py:235)         */
+    int32_t n_classes;     /*     config.n_classes          <= 32                 */
+    int32_t n_pos;         /*     rows of pos_embedding = n_tokens + 1 (fast.py:236) */
+    int32_t n_params;      /*     total fp32 elements of the flat parameter buffer */
+    int32_t zone_size[FASTB200_MAX_ZONES];   /* Cz                                              */
+    int32_t zone_off[FASTB200_MAX_ZONES];    /* prefix sum of Cz into zone_chan                 */
+    int32_t zone_chan[FASTB200_MAX_CHANS];   /* electrode row per (zone, position) -- Head.index_dict */
+    /* parameter offsets (fp32 elements) into the flat parameter / gradient buffers */
+    int32_t off_pos, off_cls;
+    int32_t off_cnn1_w[FASTB200_MAX_ZONES];  /* (F,1,1,5)  */
+    int32_t off_cnn1_b[FASTB200_MAX_ZONES];  /* (F)        */
+    int32_t off_cnn2_w[FASTB200_MAX_ZONES];  /* (F,F,Cz,1) */
+    int32_t off_cnn3_w[FASTB200_MAX_ZONES];  /* (F,F,1,5)  */
+    int32_t off_cnn4_w[FASTB200_MAX_ZONES];  /* (F,F,1,5)  */
+    int32_t off_in_w, off_in_b;              /* input_layer.0 (D, Z*F), (D) */
+    int32_t off_ln1_w[FASTB200_MAX_LAYERS], off_ln1_b[FASTB200_MAX_LAYERS];
+    int32_t off_qkv_w[FASTB200_MAX_LAYERS], off_qkv_b[FASTB200_MAX_LAYERS];   /* attn.in_proj (3D,D),(3D) */
+    int32_t off_out_w[FASTB200_MAX_LAYERS], off_out_b[FASTB200_MAX_LAYERS];   /* attn.out_proj (D,D),(D)  */
+    int32_t off_ln2_w[FASTB200_MAX_LAYERS], off_ln2_b[FASTB200_MAX_LAYERS];
+    int32_t off_ff1_w[FASTB200_MAX_LAYERS], off_ff1_b[FASTB200_MAX_LAYERS];   /* linear.0 (2D,D),(2D)     */
+    int32_t off_ff2_w[FASTB200_MAX_LAYERS], off_ff2_b[FASTB200_MAX_LAYERS];   /* linear.3 (D,2D),(D)      */
+    int32_t off_last_w, off_last_b;          /* last_layer (n_classes, D), (n_classes) */
+} fastb200_model;
+
+/* ---- library ------------------------------------------------------------------------------------------- */
+int         fastb200_version(void);
+const char* fastb200_last_error(void);
+
+/* ---- index kernels: window unfold + zone gather -------------------------------------------------------- */
+/*
+ * Replaces  x.unfold(-1, W, S) -> rearrange 'B C N T -> (B N) C T' (fast.py:247-249) followed by the per-zone
+ * gathers x[:, index_dict[area]] (fast.py:210), all zones concatenated in zone order.
+ *   x   (B, C, T) fp32          chan (n_sel) int32 electrode rows, device pointer
+ *   out (B*n_win, n_sel, W) fp32, out[b*n_win+n, j, t] = x[b, chan[j], n*S + t]       -- bit exact
+ */
+int fastb200_window_gather(const float* x, const int32_t* chan, float* out,
+                           int B, int C, int T, int W, int S, int n_win, int n_sel, void* stream);
+
+/* ---- zone embedding head (Conv4Layers x Z) -------------------------------------------------------------- */
+/* Size in floats of the packed head weights / packed head gradients for this model. */
+int64_t fastb200_head_packed_floats(const fastb200_model* m);
+/* Size in floats of the activations head_fwd saves for head_bwd: B*n_win*Z items x 3 x F x roundup4(W-4). */
+int64_t fastb200_head_saved_floats(const fastb200_model* m, int B, int n_win);
+/*
+ * Re-lays the head parameters for the kernels (run once per optimiser step): collapses cnn1 o cnn2
+ * (fast.py:113-114: no nonlinearity between them) into one (F, Cz, 5) filter + bias per zone and transposes
+ * cnn3 / cnn4 into [ci][tap][co] (forward) and [co][4-tap][ci] (input-gradient) order.
+ */
+int fastb200_head_pack(const fastb200_model* m, const float* params, float* packed, void* stream);
+/*
+ * Replaces FAST.forward_head (fast.py:242-252): unfold, zone gather, Conv4Layers for every zone, stack.
+ *   x (B, C, T)   feat (B, n_win, Z, F)   step = slide step actually used (step_override or config.slide_step)
+ *   saved: NULL for inference; else workspace of fastb200_head_saved_floats floats (y2, y3, y4 per item).
+ */
+int fastb200_head_fwd(const fastb200_model* m, const float* packed, const float* x, int B, int T, int n_win,
+                      int step, float* feat, float* saved, void* stream);
+/*
+ * Backward of the above (autograd of fast.py:111-119, 210, 247-251).
+ *   dfeat (B, n_win, Z, F)    gpacked: packed-layout weight gradients, ACCUMULATED into (caller zeroes)
+ *   dx: NULL, or (B, C, T) input gradient, ACCUMULATED into (caller zeroes)  [SHAP path, explain_fast.py:88-91]
+ */
+int fastb200_head_bwd(const fastb200_model* m, const float* packed, const float* x, const float* saved,
+                      const float* dfeat, int B, int T, int n_win, int step, float* gpacked, float* dx,
+                      void* stream);
+/* Chain rule from packed-layout gradients to d(cnn1.weight, cnn1.bias, cnn2.weight, cnn3.weight, cnn4.weight),
+ * WRITTEN (not accumulated) at the parameter offsets of `grads` (flat, same layout as params). */
+int fastb200_head_unpack_grad(const fastb200_model* m, const float* params, const float* gpacked,
+                              float* grads, void* stream);
+
+/* ---- transformer (input_layer, CLS, pos, L x AttentionBlock, last_layer) --------------------------------- */
+/* Floats saved per forward for the backward: B * (n_layers + 1) * n_tok * D  (block inputs + final tokens). */
+int64_t fastb200_transformer_saved_floats(const fastb200_model* m, int B, int n_win);
+/*
+ * Replaces FAST.forward_transformer (fast.py:260-268) and the 'train_head' branch (fast.py:273-278).
+ *   feat (B, n_win, Z, F) -> logits (B, n_classes).   mode: FASTB200_MODE_*.
+ *   dropout_p > 0 enables train-mode dropout at the four sites of fast.py:14,19,21,267 with a counter-based
+ *   generator keyed by (seed, offset); the same (seed, offset) must be given to transformer_bwd.
+ *   saved: NULL for inference.
+ */
+int fastb200_transformer_fwd(const fastb200_model* m, const float* params, const float* feat, int B, int n_win,
+                             int mode, float dropout_p, uint64_t seed, uint64_t offset,
+                             float* logits, float* saved, void* stream);
+/*
+ *   dlogits (B, n_classes)   grads: flat parameter-layout buffer, ACCUMULATED into (caller zeroes)
+ *   dfeat (B, n_win, Z, F) written (may be NULL when the head is frozen: 'train_transformer', fast.py:279-282)
+ */
+int fastb200_transformer_bwd(const fastb200_model* m, const float* params, const float* feat, const float* saved,
+                             const float* dlogits, int B, int n_win, int mode, float dropout_p, uint64_t seed,
+                             uint64_t offset, float* grads, float* dfeat, void* stream);
+
+/* ---- loss / metrics / optimiser --------------------------------------------------------------------------- */
+/*
+ * Replaces nn.CrossEntropyLoss()(logits, y) + its backward (trainer.py:37,59) and the argmax of
+ * inference_on_loader (trainer.py:89).  labels: uint8 (label_bytes = 1) or int64 (label_bytes = 8).
+ *   loss (1): mean CE.   dlogits (B, NC) = (softmax - onehot) * grad_scale / B, may be NULL.
+ *   pred (B) int64 argmax, may be NULL.   n_correct (1) int32, may be NULL.
+ */
+int fastb200_ce_fwd_bwd(const float* logits, const void* labels, int label_bytes, int B, int n_classes,
+                        float grad_scale, float* loss, float* dlogits, int64_t* pred, int32_t* n_correct,
+                        void* stream);
+/*
+ * Replaces torch.optim.AdamW(lr=5e-4).step() over all tensors (trainer.py:49): decoupled weight decay on every
+ * element, bias-corrected moments.  lr and step are read from DEVICE memory (lr (1) fp32 = base_lr * schedule
+ * factor, lr == 0 legal; step (1) int32, 1-based, incremented by the kernel when bump_step != 0), so the whole
+ * training step can sit in one CUDA graph.
+ */
+int fastb200_adamw_flat(float* p, const float* g, float* m, float* v, int64_t n, const float* lr_dev,
+                        double beta1, double beta2, double eps, double weight_decay, int32_t* step_dev,
+                        int bump_step, void* stream);
+
+/* ---- preprocessing that feeds the model ------------------------------------------------------------------ */
+/*
+ * Replaces the array math of load_subject_train_val / load_training_set / proc_one
+ * (src/fast/data/preprocess.py:57-62, 197-203): (T, C, N) MATLAB layout, fp64 (src_bytes = 8) or fp32
+ * (src_bytes = 4) -> (N, C, T_pad) fp32 with the last sample repeated (np.pad 'edge').  Bit exact.
+ */
+int fastb200_trials_from_mat(const void* src, int src_bytes, float* dst, int T, int C, int N, int T_pad,
+                             void* stream);
+/*
+ * Zero-phase IIR: scipy.signal.sosfiltfilt(sos, x, axis=-1, padtype='odd', padlen) (north_star (c); no
+ * reference implementation -- SURVEY.md section 8c).  x (rows, T) fp32 or fp64 (x_bytes), y (rows, T) fp32 or
+ * fp64 (y_bytes); sos: HOST pointer (n_sections, 6) fp64, n_sections <= 8.  Arithmetic in fp64; one warp per
+ * row, the recursion is a chunked warp-level scan.
+ */
+int fastb200_sosfiltfilt(const void* x, int x_bytes, void* y, int y_bytes, int64_t rows, int T,
+                         const double* sos_host, int n_sections, int padlen, void* stream);
+/*
+ * scipy.signal.resample_poly(x, up, down, axis=-1) with padtype='constant' (zero) edges.  h: DEVICE pointer to
+ * the already up-scaled, pre-padded fp64 FIR (len_h taps); y[j] = sum_i x[i] * h[(j+n_pre_remove)*down - i*up].
+ */
+int fastb200_resample_poly(const void* x, int x_bytes, void* y, int y_bytes, int64_t rows, int T_in, int T_out,
+                           const double* h_dev, int len_h, int up, int down, int n_pre_remove, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FASTB200_H */
