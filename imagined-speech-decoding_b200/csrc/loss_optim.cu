@@ -58,14 +58,16 @@ __global__ void ce_kernel(const float* __restrict__ logits, const LabelT* __rest
 // Scalars follow torch's single-tensor AdamW: Python-double hyper-parameter arithmetic, rounded to fp32 once
 // where torch hands them to an fp32 tensor op.
 __global__ void adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
-                             float* __restrict__ v, int64_t n, const float* __restrict__ lr_dev, double beta1,
-                             double beta2, double eps_d, double wd, const int32_t* __restrict__ step_dev, int bump) {
+                             float* __restrict__ v, int64_t n, const float* __restrict__ lr_dev, int lr_by_step,
+                             double beta1, double beta2, double eps_d, double wd,
+                             const int32_t* __restrict__ step_dev) {
     __shared__ float s_c[3];
     if (threadIdx.x == 0) {
-        const int step = *step_dev + (bump ? 1 : 0);
+        const int done = *step_dev;                  // updates already applied
+        const int step = done + 1;
         const double bc1 = 1.0 - pow(beta1, (double)step);
         const double bc2 = 1.0 - pow(beta2, (double)step);
-        const double lr = (double)*lr_dev;
+        const double lr = (double)lr_dev[lr_by_step ? done : 0];
         s_c[0] = (float)(lr / bc1);                  // step size
         s_c[1] = (float)sqrt(bc2);
         s_c[2] = (float)(1.0 - lr * wd);
@@ -126,13 +128,13 @@ extern "C" int fastb200_ce_fwd_bwd(const float* logits, const void* labels, int 
 }
 
 extern "C" int fastb200_adamw_flat(float* p, const float* g, float* m, float* v, int64_t n, const float* lr_dev,
-                                   double beta1, double beta2, double eps, double weight_decay, int32_t* step_dev,
-                                   int bump_step, void* stream) {
+                                   int lr_by_step, double beta1, double beta2, double eps, double weight_decay,
+                                   int32_t* step_dev, int bump_step, void* stream) {
     FB_REQUIRE(n >= 0, "bad n");
     if (n == 0) return 0;
     int64_t blocks = (n + 255) / 256;
     if (blocks > NUM_SMS * 8) blocks = NUM_SMS * 8;
-    adamw_kernel<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(p, g, m, v, n, lr_dev, beta1, beta2, eps, weight_decay, step_dev, bump_step);
+    adamw_kernel<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(p, g, m, v, n, lr_dev, lr_by_step, beta1, beta2, eps, weight_decay, step_dev);
     if (int r = check_launch("adamw_flat")) return r;
     if (bump_step) {
         bump_step_kernel<<<1, 1, 0, as_stream(stream)>>>(step_dev);

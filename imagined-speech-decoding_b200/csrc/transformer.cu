@@ -22,6 +22,10 @@ enum { SITE_ATTN = 0, SITE_FFN_HID = 1, SITE_FFN_OUT = 2, SITE_FINAL = 3 };
 struct DropCtx {
     float p, scale;          // p == 0 -> identity
     uint64_t seed, offset;
+    const int32_t* step_dev; // optional device counter added to offset (lets a replayed CUDA graph draw fresh masks)
+    __device__ __forceinline__ void resolve() {
+        if (p > 0.f && step_dev != nullptr) offset += (uint64_t)(uint32_t)__ldg(step_dev);
+    }
     __device__ __forceinline__ float mask(int layer, int site, int trial, int elem) const {
         if (p <= 0.f) return 1.f;
         const uint64_t idx = ((uint64_t)(layer * 4 + site) << 44) + ((uint64_t)trial << 20) + (uint64_t)elem;
@@ -277,6 +281,8 @@ __global__ void __launch_bounds__(TR_THREADS) transformer_fwd_kernel(const __gri
     const int trial0 = blockIdx.x * a.G;
     const int G = min(a.G, a.B - trial0);
     const int R = G * tok, Rmax = a.G * tok;
+    DropCtx dc = a.dc;
+    dc.resolve();
     float* Ws = smem;
     float* X = Ws + a.ws_floats;
     float* Hn = X + Rmax * D;
@@ -318,7 +324,7 @@ __global__ void __launch_bounds__(TR_THREADS) transformer_fwd_kernel(const __gri
                 a.saved[((size_t)(trial0 + g) * (m.n_layers + 1) + l) * tok * D + rem] = X[idx];
             }
         __syncthreads();
-        block_fwd<false>(m, a.params, l, bb, Wqkv, Wo, W1, W2, G, tok, a.dc, trial0);
+        block_fwd<false>(m, a.params, l, bb, Wqkv, Wo, W1, W2, G, tok, dc, trial0);
     }
     if (a.saved)
         for (int idx = threadIdx.x; idx < R * D; idx += TR_THREADS) {
@@ -331,7 +337,7 @@ __global__ void __launch_bounds__(TR_THREADS) transformer_fwd_kernel(const __gri
         const float* wl = a.params + m.off_last_w + c * D;
         float s = __ldg(a.params + m.off_last_b + c);
         for (int i = 0; i < D; ++i)
-            s = fmaf(X[(g * tok) * D + i] * a.dc.mask(0, SITE_FINAL, trial0 + g, i), __ldg(wl + i), s);
+            s = fmaf(X[(g * tok) * D + i] * dc.mask(0, SITE_FINAL, trial0 + g, i), __ldg(wl + i), s);
         a.logits[(size_t)(trial0 + g) * NC + c] = s;
     }
 }
@@ -367,7 +373,8 @@ __global__ void __launch_bounds__(TR_THREADS) transformer_bwd_kernel(const __gri
     float* stat2 = stat1 + 2 * Rmax;
     float* Fs = stat2 + 2 * Rmax;                // (G*n_win, ZF)
     float* g = a.grads;
-    const DropCtx& dc = a.dc;
+    DropCtx dc = a.dc;
+    dc.resolve();
 
     if (a.mode == FASTB200_MODE_DEFAULT) {
         // ---- classifier: logits = W_l drop(X_L[:,0]) + b_l
@@ -520,9 +527,8 @@ __global__ void __launch_bounds__(TR_THREADS) transformer_bwd_kernel(const __gri
     for (int idx = threadIdx.x; idx < Rin * D; idx += TR_THREADS) dT[idx] *= gelu_grad_f(pre[idx]);
     __syncthreads();
     linear_wgrad(dT, D, Fs, ZF, ZF, D, Rin, g + m.off_in_w, g + m.off_in_b);
-    if (a.dfeat) {
-        linear_dgrad<false>(dT, D, Ws, ZF, D, Fs, ZF, Rin);              // overwrite Fs with dfeat ... after wgrad
-    }
+    __syncthreads();                                                     // every thread is done reading Fs
+    if (a.dfeat) linear_dgrad<false>(dT, D, Ws, ZF, D, Fs, ZF, Rin);     // Fs <- dfeat
     __syncthreads();
     if (a.dfeat)
         for (int i = threadIdx.x; i < Rin * ZF; i += TR_THREADS) a.dfeat[(size_t)trial0 * n_win * ZF + i] = Fs[i];
@@ -581,13 +587,13 @@ extern "C" int64_t fastb200_transformer_saved_floats(const fastb200_model* m, in
 
 extern "C" int fastb200_transformer_fwd(const fastb200_model* m, const float* params, const float* feat, int B,
                                         int n_win, int mode, float dropout_p, uint64_t seed, uint64_t offset,
-                                        float* logits, float* saved, void* stream) {
+                                        const int32_t* dropout_step_dev, float* logits, float* saved, void* stream) {
     if (int r = validate_tr(m, B, n_win, mode, dropout_p)) return r;
     if (B == 0) return 0;
     TrArgs a{};
     a.params = params; a.feat = feat; a.logits = logits; a.saved = saved;
     a.B = B; a.n_win = n_win; a.tok = n_win + 1; a.mode = mode;
-    a.dc.p = dropout_p; a.dc.scale = dropout_p > 0.f ? 1.0f / (1.0f - dropout_p) : 1.f; a.dc.seed = seed; a.dc.offset = offset;
+    a.dc.p = dropout_p; a.dc.scale = dropout_p > 0.f ? 1.0f / (1.0f - dropout_p) : 1.f; a.dc.seed = seed; a.dc.offset = offset; a.dc.step_dev = dropout_step_dev;
     a.ws_floats = host_ws_floats(*m);
     const size_t budget = 100 * 1024;
     FB_REQUIRE(fwd_smem_floats(*m, 1, a.tok, n_win) * sizeof(float) <= 227 * 1024, "sequence too long for the shared-memory resident transformer");
@@ -601,15 +607,15 @@ extern "C" int fastb200_transformer_fwd(const fastb200_model* m, const float* pa
 
 extern "C" int fastb200_transformer_bwd(const fastb200_model* m, const float* params, const float* feat,
                                         const float* saved, const float* dlogits, int B, int n_win, int mode,
-                                        float dropout_p, uint64_t seed, uint64_t offset, float* grads, float* dfeat,
-                                        void* stream) {
+                                        float dropout_p, uint64_t seed, uint64_t offset,
+                                        const int32_t* dropout_step_dev, float* grads, float* dfeat, void* stream) {
     if (int r = validate_tr(m, B, n_win, mode, dropout_p)) return r;
     FB_REQUIRE(mode != FASTB200_MODE_DEFAULT || saved != nullptr, "transformer_bwd needs the block inputs saved by transformer_fwd");
     if (B == 0) return 0;
     TrArgs a{};
     a.params = params; a.feat = feat; a.saved = const_cast<float*>(saved); a.dlogits = dlogits; a.grads = grads; a.dfeat = dfeat;
     a.B = B; a.n_win = n_win; a.tok = n_win + 1; a.mode = mode;
-    a.dc.p = dropout_p; a.dc.scale = dropout_p > 0.f ? 1.0f / (1.0f - dropout_p) : 1.f; a.dc.seed = seed; a.dc.offset = offset;
+    a.dc.p = dropout_p; a.dc.scale = dropout_p > 0.f ? 1.0f / (1.0f - dropout_p) : 1.f; a.dc.seed = seed; a.dc.offset = offset; a.dc.step_dev = dropout_step_dev;
     a.ws_floats = host_ws_floats(*m);
     const size_t budget = 160 * 1024;
     FB_REQUIRE(bwd_smem_floats(*m, 1, a.tok, n_win) * sizeof(float) <= 227 * 1024, "sequence too long for the shared-memory resident transformer backward");

@@ -1,0 +1,110 @@
+"""ctypes binding of libfastb200.so -- the C ABI declared in include/fastb200.h.
+
+There is NO fallback: if the shared library is missing or a call fails, a RuntimeError is raised.  The library is
+plain CUDA behind ``extern "C"``; torch is used on this side only for device memory and the current stream.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+_PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_PATH = os.path.join(_PKG, "libfastb200.so")
+
+MAX_ZONES, MAX_CHANS, MAX_LAYERS = 16, 256, 16
+MODE_DEFAULT, MODE_TRAIN_HEAD = 0, 1
+
+_i32 = C.c_int32
+
+
+class ModelDesc(C.Structure):
+    """Mirror of ``struct fastb200_model`` (include/fastb200.h)."""
+    _fields_ = [
+        ("n_chan", _i32), ("window_len", _i32), ("slide_step", _i32), ("n_zones", _i32), ("dim_cnn", _i32),
+        ("dim_token", _i32), ("n_heads", _i32), ("n_layers", _i32), ("dim_hidden", _i32), ("n_classes", _i32),
+        ("n_pos", _i32), ("n_params", _i32),
+        ("zone_size", _i32 * MAX_ZONES), ("zone_off", _i32 * MAX_ZONES), ("zone_chan", _i32 * MAX_CHANS),
+        ("off_pos", _i32), ("off_cls", _i32),
+        ("off_cnn1_w", _i32 * MAX_ZONES), ("off_cnn1_b", _i32 * MAX_ZONES), ("off_cnn2_w", _i32 * MAX_ZONES),
+        ("off_cnn3_w", _i32 * MAX_ZONES), ("off_cnn4_w", _i32 * MAX_ZONES),
+        ("off_in_w", _i32), ("off_in_b", _i32),
+        ("off_ln1_w", _i32 * MAX_LAYERS), ("off_ln1_b", _i32 * MAX_LAYERS),
+        ("off_qkv_w", _i32 * MAX_LAYERS), ("off_qkv_b", _i32 * MAX_LAYERS),
+        ("off_out_w", _i32 * MAX_LAYERS), ("off_out_b", _i32 * MAX_LAYERS),
+        ("off_ln2_w", _i32 * MAX_LAYERS), ("off_ln2_b", _i32 * MAX_LAYERS),
+        ("off_ff1_w", _i32 * MAX_LAYERS), ("off_ff1_b", _i32 * MAX_LAYERS),
+        ("off_ff2_w", _i32 * MAX_LAYERS), ("off_ff2_b", _i32 * MAX_LAYERS),
+        ("off_last_w", _i32), ("off_last_b", _i32),
+    ]
+
+
+_P = C.c_void_p
+_MP = C.POINTER(ModelDesc)
+# name -> (restype, argtypes); every symbol include/fastb200.h declares
+SIGNATURES = {
+    "fastb200_version": (C.c_int, []),
+    "fastb200_last_error": (C.c_char_p, []),
+    "fastb200_window_gather": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
+    "fastb200_head_packed_floats": (C.c_int64, [_MP]),
+    "fastb200_head_saved_floats": (C.c_int64, [_MP, C.c_int, C.c_int]),
+    "fastb200_head_pack": (C.c_int, [_MP, _P, _P, _P]),
+    "fastb200_head_fwd": (C.c_int, [_MP, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P, _P]),
+    "fastb200_head_bwd": (C.c_int, [_MP, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P, _P]),
+    "fastb200_head_unpack_grad": (C.c_int, [_MP, _P, _P, _P, _P]),
+    "fastb200_transformer_saved_floats": (C.c_int64, [_MP, C.c_int, C.c_int]),
+    "fastb200_transformer_fwd": (C.c_int, [_MP, _P, _P, C.c_int, C.c_int, C.c_int, C.c_float, C.c_uint64, C.c_uint64,
+                                           _P, _P, _P, _P]),
+    "fastb200_transformer_bwd": (C.c_int, [_MP, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_float, C.c_uint64,
+                                           C.c_uint64, _P, _P, _P, _P]),
+    "fastb200_ce_fwd_bwd": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_float, _P, _P, _P, _P, _P]),
+    "fastb200_adamw_flat": (C.c_int, [_P, _P, _P, _P, C.c_int64, _P, C.c_int, C.c_double, C.c_double, C.c_double,
+                                      C.c_double, _P, C.c_int, _P]),
+    "fastb200_trials_from_mat": (C.c_int, [_P, C.c_int, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
+    "fastb200_sosfiltfilt": (C.c_int, [_P, C.c_int, _P, C.c_int, C.c_int64, C.c_int, C.POINTER(C.c_double), C.c_int,
+                                       C.c_int, _P]),
+    "fastb200_resample_poly": (C.c_int, [_P, C.c_int, _P, C.c_int, C.c_int64, C.c_int, C.c_int, _P, C.c_int, C.c_int,
+                                         C.c_int, C.c_int, _P]),
+}
+
+_lib = None
+
+
+def lib():
+    """The loaded library (loaded on first use).  Raises if it was not built: there is no CPU fallback."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python imagined-speech-decoding_b200/build.py` "
+                "(nvcc, sm_100a).  The FAST hot path has no CPU or eager-PyTorch fallback.")
+        handle = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(handle, name)          # AttributeError here = header / library mismatch: fail loudly
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def check(code: int, what: str):
+    if code != 0:
+        msg = lib().fastb200_last_error().decode(errors="replace")
+        raise RuntimeError(f"{what} failed ({code}): {msg}")
+
+
+def ptr(t):
+    """Device (or host) address of a tensor, or NULL."""
+    return None if t is None else t.data_ptr()
+
+
+def stream_ptr(device=None):
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def require_cuda(t: torch.Tensor, name: str):
+    if not t.is_cuda:
+        raise RuntimeError(
+            f"{name} is on {t.device}: the FAST hot path runs only as CUDA kernels on a B200 (sm_100a); "
+            "move the module and its input to a CUDA device (there is no CPU fallback).")

@@ -1,0 +1,543 @@
+"""FAST -- Functional Areas Spatio-Temporal Transformer, B200-native drop-in for the reference model file.
+
+Mirrors the public surface of kidusabe1/Imagined-Speech-Decoding ``src/fast/models/fast.py`` (class names, constructor
+signatures, sub-module / parameter names and construction order, forward modes -- fast.py:10-284) so that
+``FAST(config)``, ``state_dict()`` / ``load_state_dict()``, ``optim.AdamW(model.parameters())`` and the Lightning module
+of ``src/fast/train/trainer.py`` keep working unchanged.  What is different is *how* the forward and backward run:
+
+* the 94 parameters are views into ONE flat fp32 buffer in state_dict order (``_FlatParams``);
+* ``forward_head`` / ``forward_transformer`` are ``torch.autograd.Function``s whose forward AND backward are the
+  hand-written sm_100a kernels of ``libfastb200.so`` (include/fastb200.h), called through ctypes on the current CUDA
+  stream.  No ATen convolution / GEMM / attention kernel is launched for the production head (``Conv4Layers``);
+* there is no CPU path: calling the model on a CPU tensor raises.
+
+The alternative head classes of the reference (``CVBlock``, ``EEGNet_Encoder``, ``HeadConv_Paper_Version`` --
+fast.py:32-196; never used by any script) are kept as stock-PyTorch CUDA composites.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .. import _native as N
+
+__all__ = ["FAST", "AttentionBlock", "CVBlock", "Conv4Layers", "EEGNet_Encoder", "HeadConv_Paper_Version", "Head"]
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# flat parameter storage
+# ------------------------------------------------------------------------------------------------------------------
+class _FlatParams:
+    """Keeps every parameter of ``module`` as a view into one contiguous fp32 buffer (state_dict order).
+
+    ``.to()/.cuda()`` re-create the parameter tensors one by one; ``ensure()`` notices (data_ptr check) and
+    re-flattens in place (``p.data = view``), so Parameter identity -- and with it optimiser state -- survives.
+    """
+
+    def __init__(self, module: nn.Module):
+        self.module = module
+        self.flat = None
+        self.items = None          # [(name, param, offset, numel)]
+        self.offset = {}
+        self.version = 0           # bumped every time the buffer is re-created
+
+    def _collect(self):
+        items, off = [], 0
+        for name, p in self.module.named_parameters():
+            items.append((name, p, off, p.numel()))
+            off += p.numel()
+        self.items = items
+        self.offset = {name: o for name, _, o, _ in items}
+        self.total = off
+
+    def ensure(self) -> torch.Tensor:
+        if self.items is None:
+            self._collect()
+        flat = self.flat
+        ok = flat is not None
+        if ok:
+            base = flat.data_ptr()
+            for _, p, off, _ in self.items:
+                if p.data_ptr() != base + 4 * off:
+                    ok = False
+                    break
+        if not ok:
+            self._collect()
+            first = self.items[0][1]
+            for name, p, _, _ in self.items:
+                if p.dtype != torch.float32:
+                    raise RuntimeError(f"parameter {name} is {p.dtype}: the FAST kernels are fp32-only")
+                if p.device != first.device:
+                    raise RuntimeError("all FAST parameters must live on one device")
+            with torch.no_grad():
+                flat = torch.cat([p.detach().reshape(-1) for _, p, _, _ in self.items])
+                for _, p, off, n in self.items:
+                    p.data = flat[off:off + n].view(p.shape)
+            self.flat = flat
+            self.version += 1
+        return flat
+
+
+def _set_arr(arr, values):
+    for i, v in enumerate(values):
+        arr[i] = int(v)
+
+
+def _head_desc(desc: N.ModelDesc, n_chan, window_len, slide_step, zone_index, dim_cnn, offset, prefixes):
+    """Fill the head part of a model descriptor.  zone_index: list of electrode-row lists; prefixes: per-zone
+    parameter-name prefix inside the flat buffer."""
+    if len(zone_index) > N.MAX_ZONES:
+        raise RuntimeError(f"{len(zone_index)} zones: at most {N.MAX_ZONES} supported")
+    if dim_cnn not in (8, 16, 32):
+        raise RuntimeError(f"dim_cnn={dim_cnn}: the fused Conv4Layers kernels support 8, 16 or 32")
+    desc.n_chan, desc.window_len, desc.slide_step = n_chan, window_len, slide_step
+    desc.n_zones, desc.dim_cnn = len(zone_index), dim_cnn
+    sizes = [len(z) for z in zone_index]
+    if max(sizes) > 32 or min(sizes) < 1 or sum(sizes) > N.MAX_CHANS:
+        raise RuntimeError("zones must hold 1..32 electrodes each")
+    offs, chans, acc = [], [], 0
+    for z in zone_index:
+        offs.append(acc)
+        acc += len(z)
+        chans.extend(int(c) for c in z)
+    if chans and (min(chans) < 0 or max(chans) >= n_chan):
+        raise IndexError("zone electrode index out of range for the input's channel dimension")
+    _set_arr(desc.zone_size, sizes)
+    _set_arr(desc.zone_off, offs)
+    _set_arr(desc.zone_chan, chans)
+    _set_arr(desc.off_cnn1_w, [offset[p + "cnn1.weight"] for p in prefixes])
+    _set_arr(desc.off_cnn1_b, [offset[p + "cnn1.bias"] for p in prefixes])
+    _set_arr(desc.off_cnn2_w, [offset[p + "cnn2.weight"] for p in prefixes])
+    _set_arr(desc.off_cnn3_w, [offset[p + "cnn3.weight"] for p in prefixes])
+    _set_arr(desc.off_cnn4_w, [offset[p + "cnn4.weight"] for p in prefixes])
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# autograd bridges (forward and backward are both libfastb200 kernels)
+# ------------------------------------------------------------------------------------------------------------------
+def _f32c(t: torch.Tensor) -> torch.Tensor:
+    t = t.detach()
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t if t.is_contiguous() else t.contiguous()
+
+
+class _HeadFn(torch.autograd.Function):
+    """x (B,C,T) -> feat (B,n_win,Z,F): fastb200_head_pack / head_fwd; backward head_bwd / head_unpack_grad."""
+
+    @staticmethod
+    def forward(ctx, x, desc, flat, offsets, step, *params):
+        lib = N.lib()
+        N.require_cuda(x, "input")
+        xin = _f32c(x)
+        if xin.device != flat.device:
+            raise RuntimeError(f"input on {xin.device} but parameters on {flat.device}")
+        B, C, T = xin.shape
+        W = desc.window_len
+        if C != desc.n_chan:
+            raise RuntimeError(f"expected {desc.n_chan} channels, got {C}")
+        if T < W:
+            raise RuntimeError(f"maximum size for tensor at dimension 2 is {T} but size is {W}")   # Tensor.unfold's error
+        n_win = (T - W) // step + 1
+        Z, Fd = desc.n_zones, desc.dim_cnn
+        need_grad = any(ctx.needs_input_grad)
+        with torch.cuda.device(xin.device):
+            st = N.stream_ptr(xin.device)
+            packed = torch.empty(lib.fastb200_head_packed_floats(desc), device=xin.device, dtype=torch.float32)
+            N.check(lib.fastb200_head_pack(desc, N.ptr(flat), N.ptr(packed), st), "head_pack")
+            feat = torch.empty(B, n_win, Z, Fd, device=xin.device, dtype=torch.float32)
+            saved = None
+            if need_grad:
+                saved = torch.empty(lib.fastb200_head_saved_floats(desc, B, n_win), device=xin.device, dtype=torch.float32)
+            N.check(lib.fastb200_head_fwd(desc, N.ptr(packed), N.ptr(xin), B, T, n_win, step, N.ptr(feat), N.ptr(saved), st),
+                    "head_fwd")
+        ctx.desc, ctx.flat, ctx.offsets, ctx.step, ctx.n_win = desc, flat, offsets, step, n_win
+        ctx.xin, ctx.packed, ctx.saved = xin, packed, saved
+        ctx.shapes = [p.shape for p in params]
+        return feat
+
+    @staticmethod
+    def backward(ctx, dfeat):
+        lib = N.lib()
+        desc, flat, xin = ctx.desc, ctx.flat, ctx.xin
+        B, C, T = xin.shape
+        dfeat = _f32c(dfeat)
+        need_dx = ctx.needs_input_grad[0]
+        with torch.cuda.device(xin.device):
+            st = N.stream_ptr(xin.device)
+            gpacked = torch.zeros_like(ctx.packed)
+            dx = torch.zeros_like(xin) if need_dx else None
+            N.check(lib.fastb200_head_bwd(desc, N.ptr(ctx.packed), N.ptr(xin), N.ptr(ctx.saved), N.ptr(dfeat), B, T,
+                                          ctx.n_win, ctx.step, N.ptr(gpacked), N.ptr(dx), st), "head_bwd")
+            gflat = torch.empty_like(flat)
+            N.check(lib.fastb200_head_unpack_grad(desc, N.ptr(flat), N.ptr(gpacked), N.ptr(gflat), st), "head_unpack_grad")
+        grads = []
+        for off, shape, need in zip(ctx.offsets, ctx.shapes, ctx.needs_input_grad[5:]):
+            n = 1
+            for s in shape:
+                n *= s
+            grads.append(gflat[off:off + n].view(shape) if need else None)
+        return (dx, None, None, None, None, *grads)
+
+
+class _TransformerFn(torch.autograd.Function):
+    """feat (B,n_win,Z,F) -> logits (B,n_classes): fastb200_transformer_fwd / _bwd."""
+
+    @staticmethod
+    def forward(ctx, feat, desc, flat, offsets, used, mode, p_drop, seed, offset, *params):
+        lib = N.lib()
+        N.require_cuda(feat, "features")
+        fin = _f32c(feat)
+        if fin.device != flat.device:
+            raise RuntimeError(f"features on {fin.device} but parameters on {flat.device}")
+        B, n_win = fin.shape[0], fin.shape[1]
+        need_grad = any(ctx.needs_input_grad)
+        with torch.cuda.device(fin.device):
+            st = N.stream_ptr(fin.device)
+            logits = torch.empty(B, desc.n_classes, device=fin.device, dtype=torch.float32)
+            saved = None
+            if need_grad and mode == N.MODE_DEFAULT:
+                saved = torch.empty(lib.fastb200_transformer_saved_floats(desc, B, n_win), device=fin.device,
+                                    dtype=torch.float32)
+            N.check(lib.fastb200_transformer_fwd(desc, N.ptr(flat), N.ptr(fin), B, n_win, mode, p_drop, seed, offset,
+                                                 None, N.ptr(logits), N.ptr(saved), st), "transformer_fwd")
+        ctx.desc, ctx.flat, ctx.offsets, ctx.used, ctx.mode = desc, flat, offsets, used, mode
+        ctx.drop = (p_drop, seed, offset)
+        ctx.fin, ctx.saved = fin, saved
+        ctx.shapes = [p.shape for p in params]
+        return logits
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        lib = N.lib()
+        desc, flat, fin = ctx.desc, ctx.flat, ctx.fin
+        B, n_win = fin.shape[0], fin.shape[1]
+        dlogits = _f32c(dlogits)
+        need_dfeat = ctx.needs_input_grad[0]
+        p_drop, seed, offset = ctx.drop
+        with torch.cuda.device(fin.device):
+            st = N.stream_ptr(fin.device)
+            gflat = torch.zeros_like(flat)
+            dfeat = torch.empty_like(fin) if need_dfeat else None
+            N.check(lib.fastb200_transformer_bwd(desc, N.ptr(flat), N.ptr(fin), N.ptr(ctx.saved), N.ptr(dlogits), B, n_win,
+                                                 ctx.mode, p_drop, seed, offset, None, N.ptr(gflat), N.ptr(dfeat), st),
+                    "transformer_bwd")
+        grads = []
+        for off, shape, need, used in zip(ctx.offsets, ctx.shapes, ctx.needs_input_grad[9:], ctx.used):
+            n = 1
+            for s in shape:
+                n *= s
+            grads.append(gflat[off:off + n].view(shape) if (need and used) else None)
+        return (dfeat, None, None, None, None, None, None, None, None, *grads)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# modules (names, constructor order and parameter shapes follow the reference -> identical RNG use and state_dict)
+# ------------------------------------------------------------------------------------------------------------------
+class AttentionBlock(nn.Module):
+    """Pre-LN transformer block (reference fast.py:10-29).  Inside FAST it is executed by the fused transformer
+    kernel; called on its own it runs as a one-block instance of the same kernel family via ATen ops."""
+
+    def __init__(self, embed_dim, hidden_dim, num_heads, dropout=0.0):
+        super().__init__()
+        self.layer_norm_1 = nn.LayerNorm(embed_dim)
+        self.attn = nn.MultiheadAttention(embed_dim, num_heads, dropout=dropout, batch_first=True)
+        self.layer_norm_2 = nn.LayerNorm(embed_dim)
+        self.linear = nn.Sequential(
+            nn.Linear(embed_dim, hidden_dim),
+            nn.GELU(),
+            nn.Dropout(dropout),
+            nn.Linear(hidden_dim, embed_dim),
+            nn.Dropout(dropout),
+        )
+
+    def forward(self, x):
+        # stand-alone use only (FAST never calls this; it hands the whole stack to fastb200_transformer_fwd)
+        N.require_cuda(x, "input")
+        h = self.layer_norm_1(x)
+        x = x + self.attn(h, h, h, need_weights=False)[0]
+        return x + self.linear(self.layer_norm_2(x))
+
+
+class Conv4Layers(nn.Module):
+    """Per-zone temporal/spatial embedding (reference fast.py:103-119): parameter container for the fused head."""
+
+    def __init__(self, channels, dim=32):
+        super().__init__()
+        self.cnn1 = nn.Conv2d(1, dim, (1, 5), bias=True)
+        self.cnn2 = nn.Conv2d(dim, dim, (channels, 1), padding=0, bias=False)
+        self.cnn3 = nn.Conv2d(dim, dim, (1, 5), padding=(0, 2), bias=False)
+        self.cnn4 = nn.Conv2d(dim, dim, (1, 5), padding=(0, 2), bias=False)
+        self._channels, self._dim = channels, dim
+        self._fp = None
+
+    def forward(self, x):
+        """x (R, Cz, T) -> (R, dim); the whole trial is one window and the zone is every row of x."""
+        if self._fp is None:
+            self._fp = _FlatParams(self)
+        flat = self._fp.ensure()
+        desc = N.ModelDesc()
+        _head_desc(desc, x.shape[1], x.shape[2], 1, [list(range(self._channels))], self._dim, self._fp.offset, [""])
+        desc.n_params = self._fp.total
+        names = ["cnn1.weight", "cnn1.bias", "cnn2.weight", "cnn3.weight", "cnn4.weight"]
+        params = [dict(self.named_parameters())[n] for n in names]
+        feat = _HeadFn.apply(x, desc, flat, [self._fp.offset[n] for n in names], 1, *params)
+        return feat.reshape(x.shape[0], self._dim)
+
+
+class CVBlock(nn.Module):
+    """EEGNet-style zone encoder with a flatten + Linear projector (reference fast.py:32-100).  Stock PyTorch ops."""
+
+    def __init__(self, n_channels, dim_token, dropout=0.5):
+        super().__init__()
+        self.C, self.F1, self.D, self.F2, self.Kc, self.Kc2 = n_channels, 8, 2, 16, 64, 16
+        self.conv1 = nn.Conv2d(1, self.F1, (1, self.Kc), padding=(0, self.Kc // 2), bias=False)
+        self.bn1 = nn.BatchNorm2d(self.F1)
+        self.conv2 = nn.Conv2d(self.F1, self.F1 * self.D, (self.C, 1), groups=self.F1, bias=False)
+        self.bn2 = nn.BatchNorm2d(self.F1 * self.D)
+        self.act1 = nn.ELU()
+        self.pool1 = nn.AvgPool2d((1, 8))
+        self.dropout1 = nn.Dropout(dropout)
+        self.conv3 = nn.Conv2d(self.F1 * self.D, self.F2, (1, self.Kc2), padding=(0, self.Kc2 // 2), bias=False)
+        self.bn3 = nn.BatchNorm2d(self.F2)
+        self.act2 = nn.ELU()
+        self.pool2 = nn.AvgPool2d((1, 2))
+        self.dropout2 = nn.Dropout(dropout)
+        # pooled length for the reference's fixed 250-sample probe (fast.py:66-76), in closed form
+        t = 250 + 2 * (self.Kc // 2) - self.Kc + 1
+        t = t // 8
+        t = t + 2 * (self.Kc2 // 2) - self.Kc2 + 1
+        t = t // 2
+        self.flat_dim = self.F2 * t
+        self.projector = nn.Linear(self.flat_dim, dim_token)
+
+    def forward(self, x):
+        if x.dim() == 3:
+            x = x.unsqueeze(1)
+        x = self.bn1(self.conv1(x))
+        x = self.dropout1(self.pool1(self.act1(self.bn2(self.conv2(x)))))
+        x = self.dropout2(self.pool2(self.act2(self.bn3(self.conv3(x)))))
+        return self.projector(x.flatten(start_dim=1))
+
+
+class EEGNet_Encoder(nn.Module):
+    """EEGNet zone encoder with global average pooling (reference fast.py:122-167).  Stock PyTorch ops."""
+
+    def __init__(self, in_channels, feature_dim, kernel_length=64, dropout=0.25):
+        super().__init__()
+        self.F1, self.D = 8, 2
+        self.F2 = self.F1 * self.D
+        self.temporal_conv = nn.Sequential(
+            nn.Conv2d(1, self.F1, (1, kernel_length), padding=(0, kernel_length // 2), bias=False),
+            nn.BatchNorm2d(self.F1))
+        self.spatial_conv = nn.Sequential(
+            nn.Conv2d(self.F1, self.F2, (in_channels, 1), groups=self.F1, bias=False),
+            nn.BatchNorm2d(self.F2), nn.ELU(), nn.AvgPool2d((1, 4)), nn.Dropout(dropout))
+        self.separable_conv = nn.Sequential(
+            nn.Conv2d(self.F2, self.F2, (1, 16), padding=(0, 8), groups=self.F2, bias=False),
+            nn.Conv2d(self.F2, self.F2, (1, 1), bias=False),
+            nn.BatchNorm2d(self.F2), nn.ELU(), nn.AvgPool2d((1, 8)), nn.Dropout(dropout))
+        self.projector = nn.Sequential(nn.AdaptiveAvgPool2d((1, 1)), nn.Flatten(), nn.Linear(self.F2, feature_dim))
+
+    def forward(self, x):
+        return self.projector(self.separable_conv(self.spatial_conv(self.temporal_conv(x.unsqueeze(1)))))
+
+
+class HeadConv_Paper_Version(nn.Module):
+    """Four conv(k=3)+BatchNorm+GELU+maxpool stages, then a temporal mean (reference fast.py:170-196)."""
+
+    def __init__(self, in_channels, feature_dim=32):
+        super().__init__()
+        f1, f2, f3, f4 = feature_dim // 2, feature_dim // 3, feature_dim // 3, feature_dim
+        self.cnn1_t = nn.Conv2d(1, f1, (1, 3), bias=True)
+        self.cnn1_s = nn.Conv2d(f1, f1, (in_channels, 1), padding=0, bias=False)
+        self.norm1 = nn.BatchNorm2d(f1)
+        self.cnn2 = nn.Conv2d(f1, f2, (1, 3), bias=False)
+        self.norm2 = nn.BatchNorm2d(f2)
+        self.cnn3 = nn.Conv2d(f2, f3, (1, 3), bias=False)
+        self.norm3 = nn.BatchNorm2d(f3)
+        self.cnn4 = nn.Conv2d(f3, f4, (1, 3), bias=False)
+        self.norm4 = nn.BatchNorm2d(f4)
+
+    def forward(self, x):
+        x = self.cnn1_s(self.cnn1_t(x.unsqueeze(1)))
+        for norm, conv in ((self.norm1, self.cnn2), (self.norm2, self.cnn3), (self.norm3, self.cnn4), (self.norm4, None)):
+            x = F.max_pool2d(F.gelu(norm(x)), (1, 2), stride=(1, 2))
+            if conv is not None:
+                x = conv(x)
+        return x.mean(dim=(2, 3))
+
+
+class Head(nn.Module):
+    """One encoder per functional area (reference fast.py:199-210).  ``index_dict`` stays a plain dict of CPU int64
+    tensors (not a buffer, not in the state_dict) exactly as in the reference."""
+
+    def __init__(self, head, electrodes, zone_dict, feature_dim):
+        super().__init__()
+        self.index_dict = {}
+        Head_cls = globals()[head]
+        self.encoders = nn.ModuleDict()
+        for area, ch_names in zone_dict.items():
+            self.index_dict[area] = torch.tensor([electrodes.index(ch_name) for ch_name in ch_names])
+            self.encoders[area] = Head_cls(len(self.index_dict[area]), feature_dim)
+        self._fused = Head_cls is Conv4Layers
+        self._feature_dim = feature_dim
+        self._fp = None
+
+    def _zone_index(self):
+        return [self.index_dict[a].tolist() for a in self.encoders.keys()]
+
+    def forward(self, x):
+        """x (R, C, T) -> (R, Z, F)."""
+        if not self._fused:
+            N.require_cuda(x, "input")
+            return torch.stack([enc(x[:, self.index_dict[a].to(x.device)]) for a, enc in self.encoders.items()], dim=1)
+        if self._fp is None:
+            self._fp = _FlatParams(self)
+        flat = self._fp.ensure()
+        prefixes = [f"encoders.{a}." for a in self.encoders.keys()]
+        desc = N.ModelDesc()
+        _head_desc(desc, x.shape[1], x.shape[2], 1, self._zone_index(), self._feature_dim, self._fp.offset, prefixes)
+        desc.n_params = self._fp.total
+        named = dict(self.named_parameters())
+        names = [p + s for p in prefixes for s in ("cnn1.weight", "cnn1.bias", "cnn2.weight", "cnn3.weight", "cnn4.weight")]
+        feat = _HeadFn.apply(x, desc, flat, [self._fp.offset[n] for n in names], 1, *[named[n] for n in names])
+        return feat.reshape(x.shape[0], len(prefixes), self._feature_dim)
+
+
+class FAST(nn.Module):
+    name = 'FAST'
+
+    def __init__(self, config):
+        super().__init__()
+        self.config = config
+        electrodes = config.electrodes
+        zone_dict = config.zone_dict
+        head = config.head
+        dim_cnn = config.dim_cnn
+        dim_token = config.dim_token
+        n_classes = config.n_classes
+        num_heads = config.num_heads
+        num_layers = config.num_layers
+        dropout = config.dropout
+
+        self.n_tokens = (config.seq_len - config.window_len) // config.slide_step + 1
+
+        # construction order == reference fast.py:234-240 (same RNG stream -> same initial weights for a given seed)
+        self.head = Head(head, electrodes, zone_dict, dim_cnn)
+        self.input_layer = nn.Sequential(nn.Linear(dim_cnn * len(zone_dict), dim_token), nn.GELU())
+        self.transformer = nn.Sequential(*[AttentionBlock(dim_token, dim_token * 2, num_heads, dropout=dropout)
+                                           for _ in range(num_layers)])
+        self.pos_embedding = nn.Parameter(torch.randn(1, self.n_tokens + 1, dim_token))
+        self.cls_token = nn.Parameter(torch.randn(1, 1, dim_token))
+        self.last_layer = nn.Linear(dim_token, n_classes)
+        self.dropout = nn.Dropout(dropout)
+
+        if dim_token % num_heads != 0:
+            raise AssertionError("embed_dim must be divisible by num_heads")
+        if num_layers > N.MAX_LAYERS:
+            raise RuntimeError(f"num_layers={num_layers}: at most {N.MAX_LAYERS} supported")
+        self._p_drop = float(dropout)
+        self._fp = _FlatParams(self)
+        self._desc = None
+        self._head_names = None
+        self._tr_names = None
+
+    # -------------------------------------------------------------------------------------------- descriptor
+    def _runtime(self):
+        """(flat parameter buffer, model descriptor); rebuilt when the parameters moved."""
+        flat = self._fp.ensure()
+        if self._desc is None or self._desc_version != self._fp.version:
+            cfg, off = self.config, self._fp.offset
+            d = N.ModelDesc()
+            areas = list(self.head.encoders.keys())
+            if self.head._fused:
+                _head_desc(d, len(cfg.electrodes), cfg.window_len, cfg.slide_step, self.head._zone_index(),
+                           cfg.dim_cnn, off, [f"head.encoders.{a}." for a in areas])
+            else:
+                d.n_zones, d.dim_cnn = len(areas), cfg.dim_cnn
+            L = cfg.num_layers
+            d.dim_token, d.n_heads, d.n_layers = cfg.dim_token, cfg.num_heads, L
+            d.dim_hidden, d.n_classes, d.n_pos = 2 * cfg.dim_token, cfg.n_classes, self.n_tokens + 1
+            d.n_params = self._fp.total
+            d.off_pos, d.off_cls = off["pos_embedding"], off["cls_token"]
+            d.off_in_w, d.off_in_b = off["input_layer.0.weight"], off["input_layer.0.bias"]
+            t = "transformer.%d."
+            _set_arr(d.off_ln1_w, [off[t % l + "layer_norm_1.weight"] for l in range(L)])
+            _set_arr(d.off_ln1_b, [off[t % l + "layer_norm_1.bias"] for l in range(L)])
+            _set_arr(d.off_qkv_w, [off[t % l + "attn.in_proj_weight"] for l in range(L)])
+            _set_arr(d.off_qkv_b, [off[t % l + "attn.in_proj_bias"] for l in range(L)])
+            _set_arr(d.off_out_w, [off[t % l + "attn.out_proj.weight"] for l in range(L)])
+            _set_arr(d.off_out_b, [off[t % l + "attn.out_proj.bias"] for l in range(L)])
+            _set_arr(d.off_ln2_w, [off[t % l + "layer_norm_2.weight"] for l in range(L)])
+            _set_arr(d.off_ln2_b, [off[t % l + "layer_norm_2.bias"] for l in range(L)])
+            _set_arr(d.off_ff1_w, [off[t % l + "linear.0.weight"] for l in range(L)])
+            _set_arr(d.off_ff1_b, [off[t % l + "linear.0.bias"] for l in range(L)])
+            _set_arr(d.off_ff2_w, [off[t % l + "linear.3.weight"] for l in range(L)])
+            _set_arr(d.off_ff2_b, [off[t % l + "linear.3.bias"] for l in range(L)])
+            d.off_last_w, d.off_last_b = off["last_layer.weight"], off["last_layer.bias"]
+            self._desc, self._desc_version = d, self._fp.version
+            names = [n for n, _, _, _ in self._fp.items]
+            self._head_names = [n for n in names if n.startswith("head.")]
+            self._tr_names = [n for n in names if not n.startswith("head.")]
+            self._by_name = {n: p for n, p, _, _ in self._fp.items}
+        return flat, self._desc
+
+    # -------------------------------------------------------------------------------------------- forward paths
+    def forward_head(self, x, step_override=None):
+        """(B, C, T) -> (B, N, Z, F).  Window unfold, zone gather and the eight Conv4Layers stacks are one kernel."""
+        step = self.config.slide_step if step_override is None else step_override
+        if not self.head._fused:
+            N.require_cuda(x, "input")
+            xw = x.unfold(-1, self.config.window_len, step)
+            B, C, n, T = xw.shape
+            feat = self.head(xw.permute(0, 2, 1, 3).reshape(B * n, C, T))
+            return feat.reshape(B, n, feat.shape[1], feat.shape[2])
+        flat, desc = self._runtime()
+        names = self._head_names
+        return _HeadFn.apply(x, desc, flat, [self._fp.offset[n] for n in names], int(step),
+                             *[self._by_name[n] for n in names])
+
+    def batched_forward_head(self, x, step, batch_size):
+        return torch.cat([self.forward_head(mb, step) for mb in torch.split(x, batch_size, dim=0)], dim=0)
+
+    def _tokens_path(self, feat, mode):
+        flat, desc = self._runtime()
+        if feat.dim() != 4 or feat.shape[2] * feat.shape[3] != self.input_layer[0].in_features:
+            raise RuntimeError(f"expected features of shape (B, N, Z, F) with Z*F = {self.input_layer[0].in_features}, "
+                               f"got {tuple(feat.shape)}")
+        if mode == N.MODE_DEFAULT and feat.shape[1] != self.n_tokens:
+            # the reference fails to broadcast `x + pos_embedding[:, :n_tokens+1]` (fast.py:265)
+            raise RuntimeError(f"The size of tensor a ({feat.shape[1] + 1}) must match the size of tensor b "
+                               f"({self.n_tokens + 1}) at non-singleton dimension 1")
+        names = self._tr_names
+        if mode == N.MODE_TRAIN_HEAD:
+            used = [n.startswith("input_layer.") or n.startswith("last_layer.") for n in names]
+            p_drop = 0.0                                   # fast.py:273-278 has no dropout on this branch
+        else:
+            used = [True] * len(names)
+            p_drop = self._p_drop if self.training else 0.0
+        seed = offset = 0
+        if p_drop > 0.0:
+            # host-side counter draw: reproducible under torch.manual_seed, no device synchronisation
+            seed = torch.initial_seed() & 0x7FFFFFFFFFFFFFFF
+            offset = int(torch.randint(0, 2 ** 62, (1,)).item())
+        return _TransformerFn.apply(feat, desc, flat, [self._fp.offset[n] for n in names], used, mode, p_drop, seed,
+                                    offset, *[self._by_name[n] for n in names])
+
+    def forward_transformer(self, x):
+        """(B, N, Z, F) -> (B, n_classes): input layer, CLS, positions, all blocks and the classifier in one kernel."""
+        return self._tokens_path(x, N.MODE_DEFAULT)
+
+    def forward(self, x, forward_mode='default'):
+        if forward_mode == 'default':
+            return self.forward_transformer(self.forward_head(x))
+        elif forward_mode == 'train_head':
+            return self._tokens_path(self.forward_head(x), N.MODE_TRAIN_HEAD)
+        elif forward_mode == 'train_transformer':
+            with torch.no_grad():
+                x = self.forward_head(x)
+            return self.forward_transformer(x)
+        else:
+            raise NotImplementedError

@@ -123,18 +123,21 @@ int64_t fastb200_transformer_saved_floats(const fastb200_model* m, int B, int n_
  *   feat (B, n_win, Z, F) -> logits (B, n_classes).   mode: FASTB200_MODE_*.
  *   dropout_p > 0 enables train-mode dropout at the four sites of fast.py:14,19,21,267 with a counter-based
  *   generator keyed by (seed, offset); the same (seed, offset) must be given to transformer_bwd.
+ *   dropout_step_dev: NULL, or a device int32 whose value is added to `offset` when the kernel runs (the optimiser
+ *   step counter of fastb200_adamw_flat: a replayed CUDA graph then draws fresh masks every step).
  *   saved: NULL for inference.
  */
 int fastb200_transformer_fwd(const fastb200_model* m, const float* params, const float* feat, int B, int n_win,
                              int mode, float dropout_p, uint64_t seed, uint64_t offset,
-                             float* logits, float* saved, void* stream);
+                             const int32_t* dropout_step_dev, float* logits, float* saved, void* stream);
 /*
  *   dlogits (B, n_classes)   grads: flat parameter-layout buffer, ACCUMULATED into (caller zeroes)
  *   dfeat (B, n_win, Z, F) written (may be NULL when the head is frozen: 'train_transformer', fast.py:279-282)
  */
 int fastb200_transformer_bwd(const fastb200_model* m, const float* params, const float* feat, const float* saved,
                              const float* dlogits, int B, int n_win, int mode, float dropout_p, uint64_t seed,
-                             uint64_t offset, float* grads, float* dfeat, void* stream);
+                             uint64_t offset, const int32_t* dropout_step_dev, float* grads, float* dfeat,
+                             void* stream);
 
 /* ---- loss / metrics / optimiser --------------------------------------------------------------------------- */
 /*
@@ -148,13 +151,15 @@ int fastb200_ce_fwd_bwd(const float* logits, const void* labels, int label_bytes
                         void* stream);
 /*
  * Replaces torch.optim.AdamW(lr=5e-4).step() over all tensors (trainer.py:49): decoupled weight decay on every
- * element, bias-corrected moments.  lr and step are read from DEVICE memory (lr (1) fp32 = base_lr * schedule
- * factor, lr == 0 legal; step (1) int32, 1-based, incremented by the kernel when bump_step != 0), so the whole
- * training step can sit in one CUDA graph.
+ * element, bias-corrected moments.  lr and step are read from DEVICE memory so the whole training step can sit in
+ * one CUDA graph: step_dev (1) int32 = number of updates already applied (this call applies update step+1 and,
+ * when bump_step != 0, stores step+1 back); lr_dev fp32: the learning rate of this update is lr_dev[0] when
+ * lr_by_step == 0, else lr_dev[step] (a whole per-update schedule resident on the device -- the LambdaLR of
+ * trainer.py:50-53, base_lr * factor per optimiser step).  lr == 0 is legal.
  */
 int fastb200_adamw_flat(float* p, const float* g, float* m, float* v, int64_t n, const float* lr_dev,
-                        double beta1, double beta2, double eps, double weight_decay, int32_t* step_dev,
-                        int bump_step, void* stream);
+                        int lr_by_step, double beta1, double beta2, double eps, double weight_decay,
+                        int32_t* step_dev, int bump_step, void* stream);
 
 /* ---- preprocessing that feeds the model ------------------------------------------------------------------ */
 /*
@@ -167,7 +172,7 @@ int fastb200_trials_from_mat(const void* src, int src_bytes, float* dst, int T, 
 /*
  * Zero-phase IIR: scipy.signal.sosfiltfilt(sos, x, axis=-1, padtype='odd', padlen) (north_star (c); no
  * reference implementation -- SURVEY.md section 8c).  x (rows, T) fp32 or fp64 (x_bytes), y (rows, T) fp32 or
- * fp64 (y_bytes); sos: HOST pointer (n_sections, 6) fp64, n_sections <= 8.  Arithmetic in fp64; one warp per
+ * fp64 (y_bytes); sos: HOST pointer (n_sections, 6) fp64, n_sections <= 4.  Arithmetic in fp64; one warp per
  * row, the recursion is a chunked warp-level scan.
  */
 int fastb200_sosfiltfilt(const void* x, int x_bytes, void* y, int y_bytes, int64_t rows, int T,
