@@ -22,4 +22,5 @@ int check_launch(const char* what) {
 }  // namespace fb
 
 extern "C" int fastb200_version(void) { return 100; }
+extern "C" int fastb200_sizeof_model(void) { return (int)sizeof(fastb200_model); }
 extern "C" const char* fastb200_last_error(void) { return fb::g_err; }

@@ -45,6 +45,7 @@ _MP = C.POINTER(ModelDesc)
 # name -> (restype, argtypes); every symbol include/fastb200.h declares
 SIGNATURES = {
     "fastb200_version": (C.c_int, []),
+    "fastb200_sizeof_model": (C.c_int, []),
     "fastb200_last_error": (C.c_char_p, []),
     "fastb200_window_gather": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
     "fastb200_head_packed_floats": (C.c_int64, [_MP]),
@@ -84,6 +85,8 @@ def lib():
             fn = getattr(handle, name)          # AttributeError here = header / library mismatch: fail loudly
             fn.restype = res
             fn.argtypes = args
+        if handle.fastb200_sizeof_model() != C.sizeof(ModelDesc):
+            raise RuntimeError("fastb200_model layout mismatch between include/fastb200.h and fast/_native.py")
         _lib = handle
     return _lib
 

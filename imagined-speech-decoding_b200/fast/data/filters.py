@@ -1,0 +1,121 @@
+"""Batched zero-phase band-pass and rational resampling of EEG trials on the GPU (BASELINE.json north_star (c)).
+
+The reference repository has no filtering code; these functions are additive to ``fast.data``
+and follow ``scipy.signal.sosfiltfilt`` / ``scipy.signal.resample_poly`` semantics along the last axis.  The filter
+*design* (a handful of coefficients) is host arithmetic; every sample is touched only by the CUDA kernels
+``fastb200_sosfiltfilt`` / ``fastb200_resample_poly`` (include/fastb200.h).  There is no CPU fallback.
+"""
+import ctypes as C
+import math
+
+import numpy as np
+import torch
+
+from .. import _native as N
+
+
+def bandpass_sos(order=4, low=4.0, high=40.0, fs=250.0):
+    """Butterworth band-pass as second-order sections, (order, 6) float64 --
+    ``scipy.signal.butter(order, [low, high], 'bandpass', fs=fs, output='sos')``."""
+    from scipy import signal
+    return np.ascontiguousarray(signal.butter(order, [low, high], 'bandpass', fs=fs, output='sos'), dtype=np.float64)
+
+
+def default_padlen(sos):
+    """scipy.signal.sosfiltfilt's default edge length: 3 * (2*n_sections + 1 - min(#zero b2, #zero a2))."""
+    sos = np.asarray(sos)
+    ntaps = 2 * sos.shape[0] + 1
+    ntaps -= min(int((sos[:, 2] == 0).sum()), int((sos[:, 5] == 0).sum()))
+    return 3 * ntaps
+
+
+def _as_rows(x):
+    if not isinstance(x, torch.Tensor):
+        raise TypeError("expected a CUDA tensor")
+    N.require_cuda(x, "x")
+    if x.dtype not in (torch.float32, torch.float64):
+        x = x.float()
+    return x.contiguous()
+
+
+def _out_dtype(x, out_dtype):
+    if out_dtype is None:
+        return x.dtype
+    if out_dtype not in (torch.float32, torch.float64):
+        raise TypeError("out_dtype must be torch.float32 or torch.float64")
+    return out_dtype
+
+
+def sosfiltfilt(sos, x, padlen=None, out_dtype=None):
+    """Zero-phase forward-backward IIR cascade along the last axis of a CUDA tensor (odd extension of ``padlen``
+    samples, steady-state initial conditions), arithmetic in float64.  ``out_dtype`` defaults to ``x.dtype``
+    (scipy returns float64; pass ``torch.float64`` for that)."""
+    sos = np.ascontiguousarray(sos, dtype=np.float64)
+    if sos.ndim != 2 or sos.shape[1] != 6:
+        raise ValueError("sos must be shape (n_sections, 6)")
+    x = _as_rows(x)
+    T = x.shape[-1]
+    edge = default_padlen(sos) if padlen is None else int(padlen)
+    if T <= edge:
+        raise ValueError(f"The length of the input vector x must be greater than padlen, which is {edge}.")
+    y = torch.empty(x.shape, device=x.device, dtype=_out_dtype(x, out_dtype))
+    rows = x.numel() // T if T else 0
+    with torch.cuda.device(x.device):
+        N.check(N.lib().fastb200_sosfiltfilt(N.ptr(x), x.element_size(), N.ptr(y), y.element_size(), rows, T,
+                                             sos.ctypes.data_as(C.POINTER(C.c_double)), sos.shape[0], edge,
+                                             N.stream_ptr(x.device)), "sosfiltfilt")
+    return y
+
+
+def _kaiser_lowpass(up, down, beta=5.0):
+    """The default anti-aliasing FIR of scipy.signal.resample_poly: firwin(20*max(up,down)+1, 1/max(up,down),
+    window=('kaiser', 5.0)), scaled by ``up``."""
+    max_rate = max(up, down)
+    half = 10 * max_rate
+    m = np.arange(-half, half + 1, dtype=np.float64)
+    fc = 1.0 / max_rate
+    h = fc * np.sinc(fc * m) * np.kaiser(2 * half + 1, beta)
+    return h / h.sum() * up
+
+
+_FIR_CACHE = {}
+
+
+def resample_poly(x, up, down, window=None, out_dtype=None):
+    """Polyphase resampling by ``up/down`` along the last axis of a CUDA tensor with zero-padded edges
+    (``scipy.signal.resample_poly(x, up, down, axis=-1)`` defaults).  ``window``: optional 1-D FIR (already designed
+    for the reduced up/down, unity DC gain before the ``up`` scaling)."""
+    up, down = int(up), int(down)
+    if up < 1 or down < 1:
+        raise ValueError("up and down must be >= 1")
+    g = math.gcd(up, down)
+    up, down = up // g, down // g
+    x = _as_rows(x)
+    odt = _out_dtype(x, out_dtype)
+    if up == down == 1:
+        return x.to(odt, copy=True)
+    T_in = x.shape[-1]
+    T_out = -(-T_in * up // down)
+    h = _kaiser_lowpass(up, down) if window is None else np.asarray(window, dtype=np.float64) * up
+    half = (len(h) - 1) // 2
+    n_pre_pad = down - half % down
+    n_pre_remove = (half + n_pre_pad) // down
+    key = (x.device, up, down, None if window is None else h.tobytes())
+    h_dev = _FIR_CACHE.get(key)
+    if h_dev is None:
+        h_dev = torch.from_numpy(np.concatenate([np.zeros(n_pre_pad), h])).to(x.device)
+        _FIR_CACHE[key] = h_dev
+    y = torch.empty(*x.shape[:-1], T_out, device=x.device, dtype=odt)
+    rows = x.numel() // T_in if T_in else 0
+    with torch.cuda.device(x.device):
+        N.check(N.lib().fastb200_resample_poly(N.ptr(x), x.element_size(), N.ptr(y), y.element_size(), rows, T_in, T_out,
+                                               N.ptr(h_dev), h_dev.numel(), up, down, n_pre_remove,
+                                               N.stream_ptr(x.device)), "resample_poly")
+    return y
+
+
+def bandpass_resample(x, fs=250.0, low=4.0, high=40.0, order=4, up=4, down=5, out_dtype=torch.float32):
+    """The preprocessing chain of BASELINE.json config 3: order-``order`` Butterworth ``low``-``high`` Hz zero-phase
+    band-pass, then ``up/down`` polyphase resampling (250 -> 200 Hz by default).  The intermediate stays float64."""
+    y = sosfiltfilt(bandpass_sos(order, low, high, fs), x, out_dtype=torch.float64)
+    return resample_poly(y, up, down, out_dtype=out_dtype)

@@ -1,0 +1,205 @@
+"""Device-resident fused training / evaluation step for FAST -- the throughput path behind the reference's
+``training_step`` + ``AdamW.step`` + ``LambdaLR.step`` (src/fast/train/trainer.py:48-67).
+
+One step = nine launches of ``libfastb200.so`` kernels plus two memsets on ONE stream, no host synchronisation:
+
+    head_pack -> head_fwd -> transformer_fwd -> ce_fwd_bwd -> (zero grads) -> transformer_bwd -> head_bwd
+              -> head_unpack_grad -> adamw_flat (lr and step counter read from device memory)
+
+so the whole step is captured once per batch size into a CUDA graph and replayed.  Parameters stay the model's own
+``nn.Parameter``s (views into the flat buffer), so ``state_dict()`` / checkpoints see every update.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from .. import _native as N
+
+
+def lightning_lr_factors(cosine_lr_list):
+    """LR factor actually applied at optimiser step 1, 2, ... by the reference's ``LambdaLR`` that indexes
+    ``cosine_lr_list[global_step - 1]`` (trainer.py:50-53): the scheduler is built at ``global_step == 0`` (index -1),
+    and is stepped after each optimiser step, so step k >= 2 runs at ``cosine_lr_list[k - 2]``."""
+    s = np.asarray(cosine_lr_list, dtype=np.float64)
+    return np.concatenate(([s[-1]], s[:-1]))
+
+
+class FusedTrainer:
+    """AdamW training of a ``FAST`` model with the whole step on the GPU.
+
+    model        a ``fast.models.FAST`` on a CUDA device (production head ``Conv4Layers``)
+    lr           base learning rate (reference: 5e-4)
+    lr_factors   per-step multipliers in execution order (``lightning_lr_factors(cosine_scheduler(...))``), or None for
+                 a constant rate
+    forward_mode 'default' or 'train_head' ('train_transformer' = default with the head frozen)
+    """
+
+    def __init__(self, model, lr=5e-4, lr_factors=None, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01,
+                 forward_mode='default', use_graph=True, seed=None):
+        if not model.head._fused:
+            raise RuntimeError("FusedTrainer drives the fused Conv4Layers head only")
+        if forward_mode not in ('default', 'train_head', 'train_transformer'):
+            raise NotImplementedError(forward_mode)
+        self.model = model
+        self.lib = N.lib()
+        flat, desc = model._runtime()
+        N.require_cuda(flat, "model parameters")
+        self.device = flat.device
+        self.flat, self.desc = flat, desc
+        self.forward_mode = forward_mode
+        self.mode = N.MODE_TRAIN_HEAD if forward_mode == 'train_head' else N.MODE_DEFAULT
+        self.freeze_head = forward_mode == 'train_transformer'
+        self.betas, self.eps, self.weight_decay = betas, eps, weight_decay
+        self.use_graph = use_graph
+        dev = self.device
+        n = flat.numel()
+        self.grad = torch.zeros(n, device=dev)
+        self.exp_avg = torch.zeros(n, device=dev)
+        self.exp_avg_sq = torch.zeros(n, device=dev)
+        self.step_dev = torch.zeros(1, device=dev, dtype=torch.int32)
+        if lr_factors is None:
+            self.lr_dev = torch.tensor([lr], device=dev, dtype=torch.float32)
+            self.lr_by_step = 0
+        else:
+            self.lr_dev = torch.tensor(np.asarray(lr_factors, dtype=np.float64) * lr, device=dev, dtype=torch.float32)
+            self.lr_by_step = 1
+        self.n_sched = self.lr_dev.numel()
+        self.steps_done = 0
+        n_packed = self.lib.fastb200_head_packed_floats(desc)
+        self.packed = torch.empty(n_packed, device=dev)
+        self.gpacked = torch.zeros(n_packed, device=dev)
+        self.loss = torch.zeros(1, device=dev)
+        self.n_correct = torch.zeros(1, device=dev, dtype=torch.int32)
+        self.seed = int(torch.initial_seed() if seed is None else seed) & 0x7FFFFFFFFFFFFFFF
+        self._ws = {}          # (B, T, label dtype, train) -> workspace dict (+ graph)
+        # mask of parameters the chosen mode does not train: their gradient stays zero, but AdamW's weight decay
+        # would still move them -- the reference never hands them a .grad, so torch's AdamW skips them.
+        self._frozen = None
+        if self.freeze_head or self.mode == N.MODE_TRAIN_HEAD:
+            keep = torch.zeros(n, device=dev, dtype=torch.bool)
+            for name, _, off, cnt in model._fp.items:
+                if self.freeze_head:
+                    trained = not name.startswith("head.")
+                else:
+                    trained = name.startswith(("head.", "input_layer.", "last_layer."))
+                keep[off:off + cnt] = trained
+            self._frozen = ~keep
+            self._snapshot = flat.clone()
+
+    # ------------------------------------------------------------------------------------------ workspaces
+    def _workspace(self, B, T, label_dtype, train):
+        key = (B, T, label_dtype, train)
+        ws = self._ws.get(key)
+        if ws is not None:
+            return ws
+        d, dev, lib = self.desc, self.device, self.lib
+        n_win = (T - d.window_len) // d.slide_step + 1
+        ws = dict(B=B, T=T, n_win=n_win, graph=None,
+                  x=torch.empty(B, d.n_chan, T, device=dev),
+                  y=torch.empty(B, device=dev, dtype=label_dtype),
+                  feat=torch.empty(B, n_win, d.n_zones, d.dim_cnn, device=dev),
+                  logits=torch.empty(B, d.n_classes, device=dev),
+                  pred=torch.empty(B, device=dev, dtype=torch.int64))
+        if train:
+            ws["head_saved"] = torch.empty(lib.fastb200_head_saved_floats(d, B, n_win), device=dev)
+            ws["tr_saved"] = torch.empty(max(1, lib.fastb200_transformer_saved_floats(d, B, n_win)), device=dev)
+            ws["dlogits"] = torch.empty(B, d.n_classes, device=dev)
+            ws["dfeat"] = torch.empty_like(ws["feat"])
+        self._ws[key] = ws
+        return ws
+
+    # ------------------------------------------------------------------------------------------ launches
+    def _launch_train(self, ws):
+        lib, d, p = self.lib, self.desc, N.ptr
+        st = N.stream_ptr(self.device)
+        B, T, n_win = ws["B"], ws["T"], ws["n_win"]
+        p_drop = float(self.model._p_drop) if (self.model.training and self.mode == N.MODE_DEFAULT) else 0.0
+        N.check(lib.fastb200_head_pack(d, p(self.flat), p(self.packed), st), "head_pack")
+        N.check(lib.fastb200_head_fwd(d, p(self.packed), p(ws["x"]), B, T, n_win, d.slide_step, p(ws["feat"]),
+                                      None if self.freeze_head else p(ws["head_saved"]), st), "head_fwd")
+        N.check(lib.fastb200_transformer_fwd(d, p(self.flat), p(ws["feat"]), B, n_win, self.mode, p_drop, self.seed, 0,
+                                             p(self.step_dev), p(ws["logits"]), p(ws["tr_saved"]), st), "transformer_fwd")
+        N.check(lib.fastb200_ce_fwd_bwd(p(ws["logits"]), p(ws["y"]), ws["y"].element_size(), B, d.n_classes, 1.0,
+                                        p(self.loss), p(ws["dlogits"]), p(ws["pred"]), p(self.n_correct), st), "ce")
+        self.grad.zero_()
+        N.check(lib.fastb200_transformer_bwd(d, p(self.flat), p(ws["feat"]), p(ws["tr_saved"]), p(ws["dlogits"]), B, n_win,
+                                             self.mode, p_drop, self.seed, 0, p(self.step_dev), p(self.grad),
+                                             None if self.freeze_head else p(ws["dfeat"]), st), "transformer_bwd")
+        if not self.freeze_head:
+            self.gpacked.zero_()
+            N.check(lib.fastb200_head_bwd(d, p(self.packed), p(ws["x"]), p(ws["head_saved"]), p(ws["dfeat"]), B, T, n_win,
+                                          d.slide_step, p(self.gpacked), None, st), "head_bwd")
+            N.check(lib.fastb200_head_unpack_grad(d, p(self.flat), p(self.gpacked), p(self.grad), st), "head_unpack_grad")
+        N.check(lib.fastb200_adamw_flat(p(self.flat), p(self.grad), p(self.exp_avg), p(self.exp_avg_sq), self.flat.numel(),
+                                        p(self.lr_dev), self.lr_by_step, self.betas[0], self.betas[1], self.eps,
+                                        self.weight_decay, p(self.step_dev), 1, st), "adamw_flat")
+        if self._frozen is not None:
+            torch.where(self._frozen, self._snapshot, self.flat, out=self.flat)
+
+    def _launch_eval(self, ws):
+        lib, d, p = self.lib, self.desc, N.ptr
+        st = N.stream_ptr(self.device)
+        B, T, n_win = ws["B"], ws["T"], ws["n_win"]
+        N.check(lib.fastb200_head_pack(d, p(self.flat), p(self.packed), st), "head_pack")
+        N.check(lib.fastb200_head_fwd(d, p(self.packed), p(ws["x"]), B, T, n_win, d.slide_step, p(ws["feat"]), None, st),
+                "head_fwd")
+        N.check(lib.fastb200_transformer_fwd(d, p(self.flat), p(ws["feat"]), B, n_win, self.mode, 0.0, 0, 0, None,
+                                             p(ws["logits"]), None, st), "transformer_fwd")
+        N.check(lib.fastb200_ce_fwd_bwd(p(ws["logits"]), p(ws["y"]), ws["y"].element_size(), B, d.n_classes, 1.0,
+                                        p(self.loss), None, p(ws["pred"]), p(self.n_correct), st), "ce")
+
+    #: kernels of libfastb200.so launched per call (the memsets / frozen-parameter restore are ATen and not counted)
+    LAUNCHES_TRAIN = 9      # pack, head_fwd, tr_fwd, ce, tr_bwd, head_bwd, unpack, adamw, bump_step
+    LAUNCHES_EVAL = 4
+
+    def _run(self, x, y, train):
+        N.require_cuda(x, "x")
+        if x.dtype != torch.float32:
+            x = x.float()
+        if y.dtype not in (torch.uint8, torch.int64):
+            y = y.long()
+        ws = self._workspace(x.shape[0], x.shape[2], y.dtype, train)
+        launch = self._launch_train if train else self._launch_eval
+        with torch.cuda.device(self.device):
+            ws["x"].copy_(x, non_blocking=True)
+            ws["y"].copy_(y.to(self.device, non_blocking=True), non_blocking=True)
+            if not self.use_graph:
+                launch(ws)
+            elif ws["graph"] is None:
+                # one eager run (sets kernel attributes, warms allocators), then capture; capture itself does not
+                # execute, so the eager run IS this step and the graph serves the following ones.
+                launch(ws)
+                g = torch.cuda.CUDAGraph()
+                side = torch.cuda.Stream(self.device)
+                side.wait_stream(torch.cuda.current_stream(self.device))
+                with torch.cuda.stream(side):
+                    with torch.cuda.graph(g, stream=side):
+                        launch(ws)
+                torch.cuda.current_stream(self.device).wait_stream(side)
+                ws["graph"] = g
+            else:
+                ws["graph"].replay()
+        return ws
+
+    # ------------------------------------------------------------------------------------------ public API
+    def train_step(self, x, y):
+        """One optimiser step on batch (x (B,C,T) float32 CUDA, y (B,) uint8/int64).  Returns (loss, n_correct):
+        1-element device tensors that the NEXT call overwrites -- read them (``.item()``) only when needed."""
+        if self.lr_by_step and self.steps_done >= self.n_sched:
+            raise RuntimeError(f"LR schedule has {self.n_sched} entries; step {self.steps_done + 1} is past its end")
+        self._run(x, y, True)
+        self.steps_done += 1
+        return self.loss, self.n_correct
+
+    @torch.no_grad()
+    def eval_step(self, x, y):
+        """Forward + CE + argmax on one batch (no dropout).  Returns (loss, n_correct, pred) device tensors."""
+        ws = self._run(x, y, False)
+        return self.loss, self.n_correct, ws["pred"]
+
+    @torch.no_grad()
+    def predict(self, x):
+        """argmax class per trial, int64 CUDA tensor (the inner op of ``inference_on_loader``, trainer.py:89)."""
+        y = torch.zeros(x.shape[0], device=self.device, dtype=torch.uint8)
+        return self._run(x, y, False)["pred"]

@@ -72,6 +72,7 @@ typedef struct fastb200_model {
 
 /* ---- library ------------------------------------------------------------------------------------------- */
 int         fastb200_version(void);
+int         fastb200_sizeof_model(void);      /* sizeof(fastb200_model): lets a binding verify its struct mirror */
 const char* fastb200_last_error(void);
 
 /* ---- index kernels: window unfold + zone gather -------------------------------------------------------- */

@@ -58,6 +58,11 @@ class OracleConfig:
         return (self.seq_len - self.window_len) // self.slide_step + 1
 
 
+def n_tokens(cfg) -> int:
+    """fast.py:232 -- works for any attribute bag with the reference's config fields."""
+    return (cfg.seq_len - cfg.window_len) // cfg.slide_step + 1
+
+
 def zone_index(cfg) -> Dict[str, List[int]]:
     """fast.py:205-206 -- electrode name -> row index, per zone, in zone order."""
     return {a: [cfg.electrodes.index(ch) for ch in chs] for a, chs in cfg.zone_dict.items()}
@@ -161,7 +166,7 @@ def forward_transformer(sd, cfg, feat: Tensor) -> Tensor:
     tok = input_tokens(sd, feat)
     B = tok.shape[0]
     x = torch.cat([sd["cls_token"].expand(B, -1, -1), tok], dim=1)
-    x = x + sd["pos_embedding"][:, :cfg.n_tokens + 1]
+    x = x + sd["pos_embedding"][:, :n_tokens(cfg) + 1]
     for l in range(cfg.num_layers):
         x = attention_block(sd, f"transformer.{l}.", x, cfg.num_heads)
     return x[:, 0] @ sd["last_layer.weight"].t() + sd["last_layer.bias"]
