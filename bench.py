@@ -40,7 +40,7 @@ import torch
 # execute after the exact cnn1 o cnn2 collapse (window sharing is not used by the current head kernel).
 FLOP_INFER_DIRECT = 388_426_048
 HEAD_MAC_DIRECT_PER_WINDOW = 38_793_216
-HEAD_MAC_EXEC_PER_WINDOW = 246 * 32 * 5 * 64 + 2 * 246 * 32 * 160           # collapsed embed (sum Cz = 64) + cnn3 + cnn4
+HEAD_MAC_EXEC_PER_WINDOW = 246 * 32 * 5 * 64 + 8 * 2 * 246 * 32 * 160       # collapsed embed (sum Cz = 64) + 8 zones x (cnn3 + cnn4)
 FLOP_TRAIN_DIRECT = 1_140_087_744
 BYTES_PER_TRIAL = 64 * 795 * 4
 
