@@ -127,7 +127,7 @@ class _HeadFn(torch.autograd.Function):
     """x (B,C,T) -> feat (B,n_win,Z,F): fastb200_head_pack / head_fwd; backward head_bwd / head_unpack_grad."""
 
     @staticmethod
-    def forward(ctx, x, desc, flat, offsets, step, *params):
+    def forward(ctx, x, desc, flat, offsets, step, grad_mode, *params):
         lib = N.lib()
         N.require_cuda(x, "input")
         xin = _f32c(x)
@@ -141,7 +141,7 @@ class _HeadFn(torch.autograd.Function):
             raise RuntimeError(f"maximum size for tensor at dimension 2 is {T} but size is {W}")   # Tensor.unfold's error
         n_win = (T - W) // step + 1
         Z, Fd = desc.n_zones, desc.dim_cnn
-        need_grad = any(ctx.needs_input_grad)
+        need_grad = grad_mode and any(ctx.needs_input_grad)      # grad_mode: torch.is_grad_enabled() at the call site
         with torch.cuda.device(xin.device):
             st = N.stream_ptr(xin.device)
             packed = torch.empty(lib.fastb200_head_packed_floats(desc), device=xin.device, dtype=torch.float32)
@@ -173,26 +173,26 @@ class _HeadFn(torch.autograd.Function):
             gflat = torch.empty_like(flat)
             N.check(lib.fastb200_head_unpack_grad(desc, N.ptr(flat), N.ptr(gpacked), N.ptr(gflat), st), "head_unpack_grad")
         grads = []
-        for off, shape, need in zip(ctx.offsets, ctx.shapes, ctx.needs_input_grad[5:]):
+        for off, shape, need in zip(ctx.offsets, ctx.shapes, ctx.needs_input_grad[6:]):
             n = 1
             for s in shape:
                 n *= s
             grads.append(gflat[off:off + n].view(shape) if need else None)
-        return (dx, None, None, None, None, *grads)
+        return (dx, None, None, None, None, None, *grads)
 
 
 class _TransformerFn(torch.autograd.Function):
     """feat (B,n_win,Z,F) -> logits (B,n_classes): fastb200_transformer_fwd / _bwd."""
 
     @staticmethod
-    def forward(ctx, feat, desc, flat, offsets, used, mode, p_drop, seed, offset, *params):
+    def forward(ctx, feat, desc, flat, offsets, used, mode, p_drop, seed, offset, grad_mode, *params):
         lib = N.lib()
         N.require_cuda(feat, "features")
         fin = _f32c(feat)
         if fin.device != flat.device:
             raise RuntimeError(f"features on {fin.device} but parameters on {flat.device}")
         B, n_win = fin.shape[0], fin.shape[1]
-        need_grad = any(ctx.needs_input_grad)
+        need_grad = grad_mode and any(ctx.needs_input_grad)
         with torch.cuda.device(fin.device):
             st = N.stream_ptr(fin.device)
             logits = torch.empty(B, desc.n_classes, device=fin.device, dtype=torch.float32)
@@ -224,12 +224,12 @@ class _TransformerFn(torch.autograd.Function):
                                                  ctx.mode, p_drop, seed, offset, None, N.ptr(gflat), N.ptr(dfeat), st),
                     "transformer_bwd")
         grads = []
-        for off, shape, need, used in zip(ctx.offsets, ctx.shapes, ctx.needs_input_grad[9:], ctx.used):
+        for off, shape, need, used in zip(ctx.offsets, ctx.shapes, ctx.needs_input_grad[10:], ctx.used):
             n = 1
             for s in shape:
                 n *= s
             grads.append(gflat[off:off + n].view(shape) if (need and used) else None)
-        return (dfeat, None, None, None, None, None, None, None, None, *grads)
+        return (dfeat, None, None, None, None, None, None, None, None, None, *grads)
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -282,7 +282,7 @@ class Conv4Layers(nn.Module):
         desc.n_params = self._fp.total
         names = ["cnn1.weight", "cnn1.bias", "cnn2.weight", "cnn3.weight", "cnn4.weight"]
         params = [dict(self.named_parameters())[n] for n in names]
-        feat = _HeadFn.apply(x, desc, flat, [self._fp.offset[n] for n in names], 1, *params)
+        feat = _HeadFn.apply(x, desc, flat, [self._fp.offset[n] for n in names], 1, torch.is_grad_enabled(), *params)
         return feat.reshape(x.shape[0], self._dim)
 
 
@@ -402,7 +402,8 @@ class Head(nn.Module):
         desc.n_params = self._fp.total
         named = dict(self.named_parameters())
         names = [p + s for p in prefixes for s in ("cnn1.weight", "cnn1.bias", "cnn2.weight", "cnn3.weight", "cnn4.weight")]
-        feat = _HeadFn.apply(x, desc, flat, [self._fp.offset[n] for n in names], 1, *[named[n] for n in names])
+        feat = _HeadFn.apply(x, desc, flat, [self._fp.offset[n] for n in names], 1, torch.is_grad_enabled(),
+                             *[named[n] for n in names])
         return feat.reshape(x.shape[0], len(prefixes), self._feature_dim)
 
 
@@ -496,7 +497,7 @@ class FAST(nn.Module):
             return feat.reshape(B, n, feat.shape[1], feat.shape[2])
         flat, desc = self._runtime()
         names = self._head_names
-        return _HeadFn.apply(x, desc, flat, [self._fp.offset[n] for n in names], int(step),
+        return _HeadFn.apply(x, desc, flat, [self._fp.offset[n] for n in names], int(step), torch.is_grad_enabled(),
                              *[self._by_name[n] for n in names])
 
     def batched_forward_head(self, x, step, batch_size):
@@ -524,7 +525,7 @@ class FAST(nn.Module):
             seed = torch.initial_seed() & 0x7FFFFFFFFFFFFFFF
             offset = int(torch.randint(0, 2 ** 62, (1,)).item())
         return _TransformerFn.apply(feat, desc, flat, [self._fp.offset[n] for n in names], used, mode, p_drop, seed,
-                                    offset, *[self._by_name[n] for n in names])
+                                    offset, torch.is_grad_enabled(), *[self._by_name[n] for n in names])
 
     def forward_transformer(self, x):
         """(B, N, Z, F) -> (B, n_classes): input layer, CLS, positions, all blocks and the classifier in one kernel."""
