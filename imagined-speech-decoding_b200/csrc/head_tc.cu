@@ -1,0 +1,620 @@
+// Tensor-core (tcgen05 / TMEM) zone embedding head of FAST -- inference forward.
+//
+// Same arithmetic as head.cu (reference: FAST.forward_head src/fast/models/fast.py:242-252, Head.forward :209-210,
+// Conv4Layers.forward :111-119), mapped onto the 5th-generation tensor cores:
+//
+//   * each temporal convolution is an implicit GEMM  D[t][co] = sum_{tap,ci} A_tap[t][ci] * W[tap,ci][co]  with
+//     M = 128 time samples, N = 32 output channels, K = 5 taps x 32 channels.  Activations live in shared memory as
+//     [ci/8][row][8 x bf16] (K-major, SWIZZLE_NONE, SBO = 128 B), which is LINEAR in the row index, so the operand
+//     of tap k is the same tile with its descriptor start address advanced by k rows (16 B each): no im2col copy;
+//   * fp32 accuracy from bf16 tensor cores by operand splitting: x = x0 + x1 (+ x2) with bf16 terms, products
+//     a_i * b_j kept for i + j < NT.  The weight terms are stacked along N ([b0|b1|b2], one descriptor), so the pass
+//     over activation term a_i is ONE MMA of N = 32 * (NT - i) accumulating into TMEM columns [0, N): the epilogue
+//     adds the NT column groups.  (Measured on B200, tools/umma_probe.cu: an SS-mode M128 K16 MMA costs
+//     max(46.6, bytes/127) cycles -- issue/shared-memory bound, not tensor bound -- so stacking along N is free.)
+//   * a 246-sample window is two independent 128-row streams (rows [0,128) and [118,246)); each stream recomputes
+//     the few rows whose receptive field crosses the cut, so the streams never exchange data and ping-pong on the
+//     tensor pipe: while one stream's accumulator is drained (TMEM -> registers -> bias/mask -> bf16 split -> next
+//     layer's operand tile in shared memory), the other stream's MMAs run;
+//   * persistent CTAs, one zone per CTA (its ~50-77 KB of split weights stay resident in shared memory, fetched once
+//     by a bulk async copy); the 148 CTAs are apportioned to zones by cost so every zone walks the trial list at the
+//     same rate and the 8 zone passes over a trial hit L2, not HBM.
+//
+// Warp roles (640 threads): warps 0-7 / 8-15 epilogue of stream A / B (TMEM lane quadrant = warp % 4, column half =
+// (warp / 4) % 2), warp 16 MMA issuer (one elected thread) and TMEM allocator, warps 17-19 electrode loaders (fused
+// unfold + zone gather + split).
+#include "common.cuh"
+#include <cuda_bf16.h>
+#include <stdlib.h>
+
+namespace fb {
+namespace tc {
+
+constexpr int F = 32;                   // dim_cnn handled by this kernel
+constexpr int RY = 132;                 // rows of a conv operand tile: 2 zero rows + 128 + 2 zero rows
+constexpr int RX = 136;                 // rows of an electrode tile: 128 + 4 taps + 1 (tap-pair trick) + spare
+constexpr int EPI_WARPS = 16, MMA_WARP = 16, LOAD_WARP0 = 17, LOAD_WARPS = 3;   // 20 warps = 5 per SM sub-partition -> 96 registers per thread
+constexpr int CW = 16;                  // accumulator columns per epilogue warp (two warps share a TMEM lane quadrant)
+constexpr int THREADS = (EPI_WARPS + 1 + LOAD_WARPS) * 32;
+constexpr int EMB_CHUNKS = 10;          // K chunks (8 bf16) of the collapsed embed filter: 5 taps x 16 electrodes
+constexpr int CONV_CHUNKS = 20;         // 5 taps x 32 channels / 8
+
+__host__ __device__ constexpr int lb(int NT) { return 32 * NT * 16; }                       // bytes of one weight K chunk
+__host__ __device__ constexpr int zone_bytes(int NT) { return (EMB_CHUNKS + 2 * CONV_CHUNKS) * lb(NT) + 128; }
+__host__ __device__ constexpr int x_bytes(int NT) { return NT * 2 * RX * 16; }              // one stream's electrode tile
+__host__ __device__ constexpr int y_bytes(int NT) { return NT * 4 * RY * 16; }              // one stream's conv operand
+
+// ---- PTX wrappers ---------------------------------------------------------------------------------------------------
+__host__ __device__ constexpr uint32_t idesc_bf16(int N) {      // D fp32, A/B bf16, K-major both, M = 128
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+}
+// The MMA warp runs CONVERGED (every lane computes the same warp-uniform descriptors) and one elected lane issues:
+// a divergent `if (lane == 0)` makes ptxas wrap every UTCHMMA in a per-lane uniformisation loop (measured: 70-105
+// cycles per MMA of pure issue latency instead of the 47-cycle hardware rate).
+// low 32 bits of a K-major SWIZZLE_NONE descriptor: start address and LBO (16-byte units); the high word is constant.
+__device__ __forceinline__ uint32_t desc_lo(uint32_t saddr, uint32_t lbo_bytes) { return ((saddr & 0x3FFFFu) >> 4) | (lbo_bytes >> 4) << 16; }
+constexpr uint32_t DESC_HI = (128u >> 4) | (1u << 14);      // SBO = 128 B, descriptor version 1
+__device__ __forceinline__ void umma(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t idesc, uint32_t acc) {
+    asm volatile("{\n\t.reg .pred p, q;\n\t.reg .b64 da, db;\n\t"
+                 "elect.sync _|q, 0xffffffff;\n\t"
+                 "setp.ne.b32 p, %4, 0;\n\t"
+                 "mov.b64 da, {%1, %5};\n\t"
+                 "mov.b64 db, {%2, %5};\n\t"
+                 "@q tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p;\n\t}"
+                 ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(acc), "r"(DESC_HI) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("{\n\t.reg .pred q;\n\telect.sync _|q, 0xffffffff;\n\t"
+                 "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_ld32(uint32_t addr, float (&v)[32]) {
+    uint32_t r[32];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,"
+                 "%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                   "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+                   "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+                   "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                 : "r"(addr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+__device__ __forceinline__ void tmem_ld16(uint32_t addr, float (&v)[16]) {
+    uint32_t r[16];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                   "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                 : "r"(addr));
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// ---- bf16 operand splitting ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t pack_bf16x2(float even, float odd) {       // even -> low half (lower K index)
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(odd), "f"(even));
+    return r;
+}
+// eight fp32 -> NT uint4 of bf16 terms (term 0 = rounded value, term i = rounded residual after terms < i)
+template <int NT>
+__device__ __forceinline__ void split8(const float (&x)[8], uint4 (&out)[NT]) {
+    float r[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r[i] = x[i];
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            w[i] = pack_bf16x2(r[2 * i], r[2 * i + 1]);
+            if (t + 1 < NT) {                               // residual = value - bf16 term (exact in fp32), two lanes per FADD2
+                const float lo = __uint_as_float(w[i] << 16), hi = __uint_as_float(w[i] & 0xffff0000u);
+                unsigned long long d;
+                asm("{\n\t.reg .b64 a, b;\n\tmov.b64 a, {%1, %2};\n\tmov.b64 b, {%3, %4};\n\t"
+                    "sub.rn.f32x2 %0, a, b;\n\t}" : "=l"(d) : "f"(r[2 * i]), "f"(r[2 * i + 1]), "f"(lo), "f"(hi));
+                asm("mov.b64 {%0, %1}, %2;" : "=f"(r[2 * i]), "=f"(r[2 * i + 1]) : "l"(d));
+            }
+        }
+        out[t] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+
+// ---- packed fp32x2 arithmetic (sm_100: FFMA2 / FMUL2 / FADD2 -- one issue slot for two lanes of math) ---------------------
+// The epilogue of this kernel is bound by instruction ISSUE, not by a math pipe (ncu: issue slots ~50 % busy with every
+// warp latency-stalled; 41 % of all issued instructions were the scalar GELU), so halving the instruction count pays.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk(float a, float b) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ void unpk(f32x2 v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ float rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float ex2_approx(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+
+// Exact-form GELU x * Phi(x) on two values.  Phi(x) = 0.5 erfc(-x / sqrt 2) with erfc from Abramowitz & Stegun 7.1.26
+// (|erf error| <= 1.5e-7):  h = 0.5 erfc(|x| / sqrt 2) = t (c1 + t (c2 + t (c3 + t (c4 + t c5)))) exp(-x^2 / 2),
+// t = 1 / (1 + p |x| / sqrt 2);  gelu(x) = x (1 - h) for x >= 0 and x h for x < 0, i.e.  max(x, 0) - |x h|  for both.
+__device__ __forceinline__ void gelu2(float& x0, float& x1) {
+    const float t0 = rcp_approx(fmaf(fabsf(x0), 0.3275911f * 0.70710678118654752440f, 1.0f));
+    const float t1 = rcp_approx(fmaf(fabsf(x1), 0.3275911f * 0.70710678118654752440f, 1.0f));
+    const f32x2 t = pk(t0, t1), x = pk(x0, x1);
+    f32x2 q = fma2(t, pk(0.5f * 1.061405429f, 0.5f * 1.061405429f), pk(0.5f * -1.453152027f, 0.5f * -1.453152027f));
+    q = fma2(t, q, pk(0.5f * 1.421413741f, 0.5f * 1.421413741f));
+    q = fma2(t, q, pk(0.5f * -0.284496736f, 0.5f * -0.284496736f));
+    q = fma2(t, q, pk(0.5f * 0.254829592f, 0.5f * 0.254829592f));
+    q = mul2(q, t);
+    const f32x2 arg = mul2(mul2(x, x), pk(-0.72134752044448170368f, -0.72134752044448170368f));   // -x^2/2 * log2(e)
+    float a0, a1;
+    unpk(arg, a0, a1);
+    const f32x2 r = mul2(x, mul2(q, pk(ex2_approx(a0), ex2_approx(a1))));                            // x h
+    float r0, r1;
+    unpk(r, r0, r1);
+    x0 = fmaxf(x0, 0.f) - fabsf(r0);
+    x1 = fmaxf(x1, 0.f) - fabsf(r1);
+}
+
+// ---- weight packing --------------------------------------------------------------------------------------------------
+// per zone (zone_bytes(NT) bytes):  embed [10 chunks][32*NT rows][8 bf16] | cnn3 [20][32*NT][8] | cnn4 [20][32*NT][8] | beff fp32[32]
+//   row n = term * 32 + co.   K index of the embed filter: Czp = 16 -> kk = tap * 16 + c;  Czp = 8 -> kk = tap * 8 + c
+//   (taps padded to 6 so that one K16 MMA covers two taps);  conv K index kk = tap * 32 + ci.
+__device__ __forceinline__ void store_split(uint16_t* blk, int NT, int chunk, int n_co, int e, float v) {
+    float r = v;
+    for (int t = 0; t < NT; ++t) {
+        const __nv_bfloat16 b = __float2bfloat16_rn(r);
+        blk[((size_t)chunk * 32 * NT + t * 32 + n_co) * 8 + e] = __bfloat16_as_ushort(b);
+        r -= __bfloat162float(b);
+    }
+}
+
+__global__ void head_pack_tc_kernel(fastb200_model m, const float* __restrict__ params, uint8_t* __restrict__ packed, int NT) {
+    const int z = blockIdx.x;
+    const int Cz = m.zone_size[z];
+    const int Czp = Cz <= 8 ? 8 : 16;
+    uint8_t* zb = packed + (size_t)z * (NT == 2 ? zone_bytes(2) : zone_bytes(3));
+    uint16_t* emb = reinterpret_cast<uint16_t*>(zb);
+    uint16_t* c3 = emb + EMB_CHUNKS * 32 * NT * 8;
+    uint16_t* c4 = c3 + CONV_CHUNKS * 32 * NT * 8;
+    float* beff = reinterpret_cast<float*>(c4 + CONV_CHUNKS * 32 * NT * 8);
+    const float* w1 = params + m.off_cnn1_w[z];
+    const float* b1 = params + m.off_cnn1_b[z];
+    const float* w2 = params + m.off_cnn2_w[z];
+    const float* w3 = params + m.off_cnn3_w[z];
+    const float* w4 = params + m.off_cnn4_w[z];
+    // collapsed cnn1 o cnn2 (same summation order as head_pack_kernel in head.cu)
+    for (int i = threadIdx.x; i < EMB_CHUNKS * 8 * F; i += blockDim.x) {
+        const int f = i % F, kk = i / F;
+        const int k = kk / Czp, c = kk % Czp;
+        float s = 0.f;
+        if (k < TAPS && c < Cz)
+            for (int g = 0; g < F; ++g) s = fmaf(w2[(f * F + g) * Cz + c], w1[g * TAPS + k], s);
+        store_split(emb, NT, kk / 8, f, kk % 8, s);
+    }
+    for (int f = threadIdx.x; f < F; f += blockDim.x) {
+        float s = 0.f;
+        for (int g = 0; g < F; ++g) {
+            float r = 0.f;
+            for (int c = 0; c < Cz; ++c) r += w2[(f * F + g) * Cz + c];
+            s = fmaf(r, b1[g], s);
+        }
+        beff[f] = s;
+    }
+    for (int i = threadIdx.x; i < CONV_CHUNKS * 8 * F; i += blockDim.x) {
+        const int co = i % F, kk = i / F;
+        const int k = kk / F, ci = kk % F;
+        store_split(c3, NT, kk / 8, co, kk % 8, w3[(co * F + ci) * TAPS + k]);
+        store_split(c4, NT, kk / 8, co, kk % 8, w4[(co * F + ci) * TAPS + k]);
+    }
+}
+
+// ---- kernel arguments ------------------------------------------------------------------------------------------------
+struct FwdArgs {
+    const uint8_t* packed;
+    const float* x;
+    float* feat;
+    long long* prof;                           // PROF builds only: per-CTA wait-cycle counters [grid][16]
+    int dbg;                                   // PROF builds only: bit0 skip operand stores, bit1 skip GELU, bit2 skip electrode loads
+    int B, T, n_win, step, C, W, Z;
+    int T_out, split, tb1;                     // stream B starts at row tb1 = T_out - 128; stream A owns t < split
+    int cz[FASTB200_MAX_ZONES];
+    int zoff[FASTB200_MAX_ZONES];
+    int chan[FASTB200_MAX_CHANS];
+    uint8_t cta_zone[NUM_SMS];                 // zone of CTA c
+    uint8_t cta_rank[NUM_SMS];                 // its rank among the CTAs of that zone
+    uint8_t zone_ctas[FASTB200_MAX_ZONES];     // CTAs apportioned to each zone
+};
+
+struct Smem {                                  // fixed part at the start of dynamic shared memory
+    uint64_t w_full;
+    uint64_t x_full[2], x_empty[2], d_full[2], y_ready[2], d_free[2];
+    uint32_t tmem_base;
+    int counter[2];
+    float red[2][EPI_WARPS][CW];
+};
+constexpr int SMEM_HDR = 3072;                 // bytes reserved for Smem in front of the operand tiles
+static_assert(sizeof(Smem) <= SMEM_HDR, "Smem header overflows its reservation");
+
+// ---- forward kernel --------------------------------------------------------------------------------------------------
+template <int NT, bool PROF>
+__global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_constant__ FwdArgs a) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
+    uint8_t* wz = smem_raw + SMEM_HDR;                                  // this zone's split weights (zone_bytes(NT))
+    uint8_t* xs = wz + zone_bytes(NT);                              // [2 streams] electrode tiles
+    uint8_t* ys = xs + 2 * x_bytes(NT);                             // [2 streams] conv operand tiles
+    constexpr int LB = lb(NT);
+    constexpr int DCOLS = 32 * NT;                                  // accumulator columns per stream
+    constexpr int TMEM_COLS = 2 * DCOLS <= 128 ? 128 : 256;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int z = a.cta_zone[blockIdx.x];
+    const int rank = a.cta_rank[blockIdx.x], nz = a.zone_ctas[z];
+    const int BN = a.B * a.n_win;
+    const int Cz = a.cz[z];
+    const int n_xchunk = Cz <= 8 ? 1 : 2;
+
+    // ---- one-time setup: barriers, TMEM, weights (bulk async copy), zero rows of the operand tiles
+    if (tid == 0) {
+        mbar_init(&sm.w_full, 1);
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&sm.x_full[s], LOAD_WARPS * 32);
+            mbar_init(&sm.x_empty[s], 1);
+            mbar_init(&sm.d_full[s], 1);
+            mbar_init(&sm.y_ready[s], EPI_WARPS * 16);
+            mbar_init(&sm.d_free[s], EPI_WARPS * 16);
+        }
+        sm.counter[0] = sm.counter[1] = 0;
+        fence_mbar_init();
+    }
+    for (int i = tid; i < 2 * y_bytes(NT) / 16; i += THREADS) reinterpret_cast<uint4*>(ys)[i] = make_uint4(0, 0, 0, 0);
+    if (warp == MMA_WARP) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)), "n"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = sm.tmem_base;
+    if (rank >= BN) {                                               // nothing to do for this CTA (tiny batches)
+        __syncthreads();
+        if (warp == MMA_WARP) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS) : "memory");
+        return;
+    }
+    const int n_it = (BN - rank + nz - 1) / nz;                     // items rank, rank + nz, ...
+
+    if (warp == MMA_WARP) {
+        // =========================================== MMA issuer ===========================================
+        {
+            if (lane == 0) {
+                mbar_expect_tx(&sm.w_full, (uint32_t)zone_bytes(NT));
+                bulk_g2s(wz, a.packed + (size_t)z * zone_bytes(NT), (uint32_t)zone_bytes(NT), &sm.w_full);
+            }
+            __syncwarp();
+            mbar_wait(&sm.w_full, 0);
+            const uint32_t w_emb = smem_u32(wz), w_c3 = w_emb + EMB_CHUNKS * LB, w_c4 = w_c3 + CONV_CHUNKS * LB;
+            long long pw[4] = {0, 0, 0, 0};
+            const long long t_start = PROF ? clock64() : 0;
+            for (int it = 0; it < n_it; ++it) {
+                // collapsed cnn1 o cnn2 on the electrode tiles
+                for (int s = 0; s < 2; ++s) {
+                    long long c0 = 0, c1 = 0;
+                    if (PROF) c0 = clock64();
+                    mbar_wait(&sm.x_full[s], it & 1);
+                    if (PROF) { c1 = clock64(); pw[0] += c1 - c0; }
+                    if (it > 0) mbar_wait(&sm.d_free[s], (it - 1) & 1);
+                    if (PROF) pw[1] += clock64() - c1;
+                    tc_fence_after();
+                    const uint32_t d = tmem + s * DCOLS;
+                    const uint32_t xb = smem_u32(xs) + s * x_bytes(NT);
+                    uint32_t acc = 0;
+                    if (n_xchunk == 2) {
+#pragma unroll
+                        for (int k = 0; k < TAPS; ++k)
+#pragma unroll
+                            for (int t = 0; t < NT; ++t) {
+                                umma(d, desc_lo(xb + t * (2 * RX * 16) + k * 16, RX * 16), desc_lo(w_emb + 2 * k * LB, LB),
+                                     idesc_bf16(32 * (NT - t)), acc);
+                                acc = 1;
+                            }
+                    } else {                                        // 8 electrodes: one K16 step = taps (2p, 2p+1), LBO = one row
+#pragma unroll
+                        for (int p = 0; p < 3; ++p)
+#pragma unroll
+                            for (int t = 0; t < NT; ++t) {
+                                umma(d, desc_lo(xb + t * (2 * RX * 16) + 2 * p * 16, 16), desc_lo(w_emb + 2 * p * LB, LB),
+                                     idesc_bf16(32 * (NT - t)), acc);
+                                acc = 1;
+                            }
+                    }
+                    umma_commit(&sm.d_full[s]);
+                    umma_commit(&sm.x_empty[s]);
+                }
+                // cnn3, cnn4 on the conv operand tiles
+                for (int layer = 0; layer < 2; ++layer) {
+                    const uint32_t wl = layer == 0 ? w_c3 : w_c4;
+                    for (int s = 0; s < 2; ++s) {
+                        long long c0 = 0;
+                        if (PROF) c0 = clock64();
+                        mbar_wait(&sm.y_ready[s], layer);           // two completions per item: phase = layer
+                        if (PROF) pw[2 + layer] += clock64() - c0;
+                        tc_fence_after();
+                        const uint32_t d = tmem + s * DCOLS;
+                        const uint32_t yb = smem_u32(ys) + s * y_bytes(NT);
+                        uint32_t acc = 0;
+#pragma unroll
+                        for (int k = 0; k < TAPS; ++k)
+#pragma unroll
+                            for (int h = 0; h < 2; ++h)
+#pragma unroll
+                                for (int t = 0; t < NT; ++t) {
+                                    umma(d, desc_lo(yb + t * (4 * RY * 16) + 2 * h * (RY * 16) + k * 16, RY * 16),
+                                         desc_lo(wl + (4 * k + 2 * h) * LB, LB), idesc_bf16(32 * (NT - t)), acc);
+                                    acc = 1;
+                                }
+                        umma_commit(&sm.d_full[s]);
+                    }
+                }
+            }
+            if (PROF && lane == 0) {
+                long long* o = a.prof + (size_t)blockIdx.x * 16;
+                o[0] = clock64() - t_start; o[1] = pw[0]; o[2] = pw[1]; o[3] = pw[2]; o[4] = pw[3]; o[5] = n_it;
+            }
+        }
+    } else if (warp >= LOAD_WARP0) {
+        // ============================ electrode loaders: unfold + zone gather + split ============================
+        // Thread slot k of a stream handles tile entry i = lt + k * 96 = (electrode chunk j, row r): the same (j, r) for
+        // every item, so the eight gather offsets chan[c] * T + t are computed once, outside the item loop.
+        const int lt = tid - LOAD_WARP0 * 32;
+        const int* chan = a.chan + a.zoff[z];
+        constexpr int NLT = LOAD_WARPS * 32;
+        constexpr int SLOTS = (2 * RX + NLT - 1) / NLT;             // 3 for two electrode chunks
+        for (int it = 0; it < n_it; ++it) {
+            const int item = rank + it * nz;
+            const int b = item / a.n_win, n = item - b * a.n_win;
+            const float* xb = a.x + (size_t)b * a.C * a.T + (size_t)n * a.step;
+            for (int s = 0; s < 2; ++s) {
+                if (it > 0) mbar_wait(&sm.x_empty[s], (it - 1) & 1);
+                const int tb = s == 0 ? 0 : a.tb1;
+                uint8_t* xt = xs + s * x_bytes(NT);
+                if (!(PROF && (a.dbg & 4))) {
+                    float v[SLOTS][8];
+#pragma unroll
+                    for (int k = 0; k < SLOTS; ++k) {               // all loads of this tile in flight before the first use
+                        const int i = lt + k * NLT;
+                        const int j = i >= RX ? 1 : 0, r = i - j * RX;
+                        const int t = tb + r;
+                        const bool row_ok = i < n_xchunk * RX && t < a.W;
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            const int c = 8 * j + e;
+                            v[k][e] = (row_ok && c < Cz) ? __ldg(xb + (size_t)chan[c] * a.T + t) : 0.f;
+                        }
+                    }
+#pragma unroll
+                    for (int k = 0; k < SLOTS; ++k) {
+                        const int i = lt + k * NLT;
+                        const int j = i >= RX ? 1 : 0, r = i - j * RX;
+                        if (i < n_xchunk * RX) {
+                            uint4 o[NT];
+                            split8<NT>(v[k], o);
+#pragma unroll
+                            for (int tm = 0; tm < NT; ++tm)
+                                *reinterpret_cast<uint4*>(xt + tm * (2 * RX * 16) + j * (RX * 16) + r * 16) = o[tm];
+                        }
+                    }
+                }
+                fence_proxy_async();
+                mbar_arrive(&sm.x_full[s]);
+            }
+        }
+    } else {
+        // ============================ epilogue warps (stream s, lane quadrant q, column half h) ============================
+        const int s = warp >> 3, h = (warp >> 2) & 1, q = warp & 3;
+        const int m = 32 * q + lane;                                // accumulator row = TMEM lane
+        const int t = (s == 0 ? 0 : a.tb1) + m;                     // time sample of this row
+        const uint32_t d_addr = tmem + ((uint32_t)(32 * q) << 16) + s * DCOLS + CW * h;
+        uint8_t* yt = ys + s * y_bytes(NT) + (m + 2) * 16 + 2 * h * (RY * 16);
+        const float* beff = reinterpret_cast<const float*>(wz + (EMB_CHUNKS + 2 * CONV_CHUNKS) * LB) + CW * h;
+        const bool live = t < a.T_out;                              // rows past the window are the next conv's zero padding
+        const bool own = live && (s == 0 ? t < a.split : t >= a.split);
+        mbar_wait(&sm.w_full, 0);                                   // beff visible
+        long long ew = 0, ep[5] = {0, 0, 0, 0, 0};
+        for (int it = 0; it < n_it; ++it) {
+            for (int stage = 0; stage < 3; ++stage) {
+                long long c0 = 0;
+                if (PROF) c0 = clock64();
+                mbar_wait(&sm.d_full[s], (it + stage) & 1);         // three completions per item
+                if (PROF) ew += clock64() - c0;
+                tc_fence_after();
+                float v[CW];
+                {
+                    float u[NT - 1][CW];
+                    tmem_ld16(d_addr, v);
+#pragma unroll
+                    for (int tm = 1; tm < NT; ++tm) tmem_ld16(d_addr + 32 * tm, u[tm - 1]);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int tm = 1; tm < NT; ++tm)
+#pragma unroll
+                        for (int i = 0; i < CW; ++i) v[i] += u[tm - 1][i];
+                }
+                long long c1 = 0;
+                if (PROF) { c1 = clock64(); ep[0] += c1 - c0; }       // includes the d_full wait (subtract ew)
+                if (stage < 2) {
+                    if (!(PROF && (a.dbg & 1)))
+#pragma unroll
+                    for (int j = 0; j < CW / 8; ++j) {
+                        float x8[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            float val = v[8 * j + e];
+                            if (stage == 0) val += beff[8 * j + e];
+                            x8[e] = live ? val : 0.f;
+                        }
+                        uint4 o[NT];
+                        split8<NT>(x8, o);
+#pragma unroll
+                        for (int tm = 0; tm < NT; ++tm) *reinterpret_cast<uint4*>(yt + tm * (4 * RY * 16) + j * (RY * 16)) = o[tm];
+                    }
+                    long long c2 = 0;
+                    if (PROF) { c2 = clock64(); ep[1] += c2 - c1; }
+                    fence_proxy_async();
+                    if (PROF) ep[2] += clock64() - c2;
+                    tc_fence_before();
+                    mbar_arrive(&sm.y_ready[s]);
+                } else {
+                    tc_fence_before();
+                    mbar_arrive(&sm.d_free[s]);                     // accumulator drained: next item's embed may overwrite it
+#pragma unroll
+                    for (int i = 0; i < CW; i += 2) {
+                        v[i] = own ? v[i] : 0.f;                    // gelu(0) == 0: rows this stream does not own add nothing
+                        v[i + 1] = own ? v[i + 1] : 0.f;
+                        if (!(PROF && (a.dbg & 2))) gelu2(v[i], v[i + 1]);
+                    }
+                    // sum over the warp's 32 rows by recursive halving (16 shuffles): lanes 2c, 2c+1 end up with column c
+#pragma unroll
+                    for (int st = 16; st >= 2; st >>= 1) {
+                        const bool upper = (lane & st) != 0;
+#pragma unroll
+                        for (int i = 0; i < st / 2; ++i) {
+                            const float keep = upper ? v[i + st / 2] : v[i];
+                            const float send = upper ? v[i] : v[i + st / 2];
+                            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, st);
+                        }
+                    }
+                    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+                    long long c3 = 0;
+                    if (PROF) { c3 = clock64(); ep[3] += c3 - c1; }
+                    const int par = it & 1;
+                    if ((lane & 1) == 0) sm.red[par][warp][lane >> 1] = v[0];
+                    __syncwarp();
+                    int old = 0;
+                    if (lane == 0) {
+                        __threadfence_block();
+                        old = atomicAdd(&sm.counter[par], 1);
+                    }
+                    old = __shfl_sync(0xffffffffu, old, 0);
+                    if (old == EPI_WARPS - 1) {                     // last of the 16 warps: fixed-order sum -> deterministic
+                        __threadfence_block();
+                        float tot = 0.f;                            // lane = output channel co = 16 h' + c
+#pragma unroll
+                        for (int ss = 0; ss < 2; ++ss)
+#pragma unroll
+                            for (int qq = 0; qq < 4; ++qq) tot += sm.red[par][ss * 8 + (lane >> 4) * 4 + qq][lane & 15];
+                        const int item = rank + it * nz;
+                        a.feat[((size_t)item * a.Z + z) * F + lane] = tot / (float)a.T_out;
+                        __syncwarp();
+                        if (lane == 0) sm.counter[par] = 0;
+                    }
+                    if (PROF) ep[4] += clock64() - c3;
+                }
+            }
+        }
+        if (PROF && tid == 0) { long long* o = a.prof + (size_t)blockIdx.x * 16; o[6] = ew; o[8] = ep[0]; o[9] = ep[1]; o[10] = ep[2]; o[11] = ep[3]; o[12] = ep[4]; }
+        if (PROF && tid == 256) a.prof[(size_t)blockIdx.x * 16 + 7] = ew;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == MMA_WARP) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS) : "memory");
+}
+
+}  // namespace tc
+}  // namespace fb
+
+// ---- host side -------------------------------------------------------------------------------------------------------
+using namespace fb;
+
+static int tc_supported(const fastb200_model* m, int n_terms) {
+    FB_REQUIRE(m != nullptr, "model descriptor is NULL");
+    FB_REQUIRE(n_terms == 2 || n_terms == 3, "n_terms=%d: the split-bf16 head supports 2 or 3 terms", n_terms);
+    FB_REQUIRE(m->dim_cnn == tc::F, "tensor-core head needs dim_cnn == 32 (got %d)", m->dim_cnn);
+    FB_REQUIRE(m->n_zones >= 1 && m->n_zones <= FASTB200_MAX_ZONES, "n_zones=%d out of range", m->n_zones);
+    const int T_out = m->window_len - 4;
+    FB_REQUIRE(T_out >= 128 && T_out <= 248, "tensor-core head needs 132 <= window_len <= 252 (got %d)", m->window_len);
+    for (int z = 0; z < m->n_zones; ++z)
+        FB_REQUIRE(m->zone_size[z] >= 1 && m->zone_size[z] <= 16, "zone %d has %d electrodes (tensor-core head: 1..16)", z, m->zone_size[z]);
+    return 0;
+}
+
+extern "C" int fastb200_head_tc_supported(const fastb200_model* m) { return tc_supported(m, 2) == 0 ? 1 : 0; }
+
+extern "C" int64_t fastb200_head_packed_tc_bytes(const fastb200_model* m, int n_terms) {
+    if (tc_supported(m, n_terms)) return -1;
+    return (int64_t)m->n_zones * tc::zone_bytes(n_terms);
+}
+
+extern "C" int fastb200_head_pack_tc(const fastb200_model* m, const float* params, void* packed, int n_terms, void* stream) {
+    if (int r = tc_supported(m, n_terms)) return r;
+    tc::head_pack_tc_kernel<<<m->n_zones, 256, 0, as_stream(stream)>>>(*m, params, static_cast<uint8_t*>(packed), n_terms);
+    return check_launch("head_pack_tc");
+}
+
+// Diagnostic buffer for the next fastb200_head_fwd_tc calls of this thread (148 x 8 int64 wait-cycle counters per launch);
+// NULL (default) = uninstrumented kernel.  Not part of the product path.
+static thread_local long long* g_tc_prof = nullptr;
+extern "C" void fastb200_debug_set_tc_profile(long long* dev_buf) { g_tc_prof = dev_buf; }
+
+extern "C" int fastb200_head_fwd_tc(const fastb200_model* m, const void* packed, const float* x, int B, int T, int n_win,
+                                    int step, float* feat, int n_terms, void* stream) {
+    if (int r = tc_supported(m, n_terms)) return r;
+    FB_REQUIRE(B >= 0 && n_win >= 1 && step >= 1, "bad B/n_win/step");
+    FB_REQUIRE((n_win - 1) * (int64_t)step + m->window_len <= T, "windows run past the trial: n_win=%d step=%d W=%d T=%d", n_win, step, m->window_len, T);
+    FB_REQUIRE((int64_t)B * n_win < (1ll << 31) / FASTB200_MAX_ZONES, "too many items for one launch");
+    if (B == 0) return 0;
+    tc::FwdArgs a;
+    a.packed = static_cast<const uint8_t*>(packed); a.x = x; a.feat = feat; a.prof = g_tc_prof;
+    a.dbg = (g_tc_prof && getenv("FASTB200_TC_DBG")) ? atoi(getenv("FASTB200_TC_DBG")) : 0;
+    a.B = B; a.T = T; a.n_win = n_win; a.step = step; a.C = m->n_chan; a.W = m->window_len; a.Z = m->n_zones;
+    a.T_out = m->window_len - 4; a.split = a.T_out / 2; a.tb1 = a.T_out - 128;
+    int n_sel = 0;
+    for (int z = 0; z < m->n_zones; ++z) { a.cz[z] = m->zone_size[z]; a.zoff[z] = m->zone_off[z]; n_sel += m->zone_size[z]; }
+    for (int i = 0; i < n_sel; ++i) a.chan[i] = m->zone_chan[i];
+    // apportion the CTAs to zones in proportion to per-item MMA cost (largest remainder), at least one each
+    const int Z = m->n_zones;
+    const int grid = NUM_SMS >= Z ? NUM_SMS : Z;
+    double cost[FASTB200_MAX_ZONES], total = 0;
+    for (int z = 0; z < Z; ++z) { cost[z] = 20.0 + (m->zone_size[z] <= 8 ? 3.0 : 5.0); total += cost[z]; }
+    int n_cta[FASTB200_MAX_ZONES], used = 0;
+    double frac[FASTB200_MAX_ZONES];
+    for (int z = 0; z < Z; ++z) {
+        const double share = cost[z] / total * grid;
+        n_cta[z] = (int)share < 1 ? 1 : (int)share;
+        frac[z] = share - n_cta[z];
+        used += n_cta[z];
+    }
+    while (used < grid) {
+        int best = 0;
+        for (int z = 1; z < Z; ++z) if (frac[z] > frac[best]) best = z;
+        n_cta[best]++; frac[best] -= 1.0; used++;
+    }
+    while (used > grid) {                                    // only when the minimum of one CTA per zone overshoots
+        int best = 0;
+        for (int z = 1; z < Z; ++z) if (n_cta[z] > n_cta[best]) best = z;
+        n_cta[best]--; used--;
+    }
+    // interleave the zones over the CTA index so that co-resident waves mix zones
+    int given[FASTB200_MAX_ZONES] = {0};
+    int c = 0;
+    while (c < grid)
+        for (int z = 0; z < Z && c < grid; ++z)
+            if (given[z] < n_cta[z]) { a.cta_zone[c] = (uint8_t)z; a.cta_rank[c] = (uint8_t)given[z]++; ++c; }
+    for (int z = 0; z < Z; ++z) a.zone_ctas[z] = (uint8_t)n_cta[z];
+    const size_t smem = tc::SMEM_HDR + tc::zone_bytes(n_terms) + 2 * tc::x_bytes(n_terms) + 2 * tc::y_bytes(n_terms);
+    cudaError_t e;
+#define LAUNCH_TC(NTT, PROFF)                                                                                      \
+    e = cudaFuncSetAttribute(tc::head_fwd_tc_kernel<NTT, PROFF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+    if (e != cudaSuccess) return fail((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));                 \
+    tc::head_fwd_tc_kernel<NTT, PROFF><<<grid, tc::THREADS, smem, as_stream(stream)>>>(a);
+    if (a.prof) { if (n_terms == 2) { LAUNCH_TC(2, true) } else { LAUNCH_TC(3, true) } }
+    else        { if (n_terms == 2) { LAUNCH_TC(2, false) } else { LAUNCH_TC(3, false) } }
+#undef LAUNCH_TC
+    return check_launch("head_fwd_tc");
+}

@@ -16,13 +16,35 @@ fast.py:32-196; never used by any script) are kept as stock-PyTorch CUDA composi
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
 from .. import _native as N
 
-__all__ = ["FAST", "AttentionBlock", "CVBlock", "Conv4Layers", "EEGNet_Encoder", "HeadConv_Paper_Version", "Head"]
+__all__ = ["FAST", "AttentionBlock", "CVBlock", "Conv4Layers", "EEGNet_Encoder", "HeadConv_Paper_Version", "Head",
+           "set_head_precision", "get_head_precision"]
+
+# Arithmetic of the Conv4Layers head when no gradient is needed (inference):
+#   'bf16x3'  tcgen05 tensor cores, every fp32 operand split into 3 bf16 terms (24 mantissa bits, fp32-equivalent)
+#   'bf16x2'  tcgen05 tensor cores, 2 bf16 terms (16 mantissa bits; features still ~1e-6: they are 246-sample means)
+#   'fp32'    CUDA-core FFMA kernel (also what every shape the tensor-core kernel does not cover falls to, and what
+#             training uses: its forward saves the activations the backward kernel needs)
+_HEAD_PRECISION = os.environ.get("FASTB200_HEAD_PRECISION", "bf16x3")
+_TERMS = {"bf16x3": 3, "bf16x2": 2, "fp32": 0}
+
+
+def set_head_precision(mode: str):
+    global _HEAD_PRECISION
+    if mode not in _TERMS:
+        raise ValueError(f"head precision must be one of {sorted(_TERMS)}, got {mode!r}")
+    _HEAD_PRECISION = mode
+
+
+def get_head_precision() -> str:
+    return _HEAD_PRECISION
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -144,9 +166,19 @@ class _HeadFn(torch.autograd.Function):
         need_grad = grad_mode and any(ctx.needs_input_grad)      # grad_mode: torch.is_grad_enabled() at the call site
         with torch.cuda.device(xin.device):
             st = N.stream_ptr(xin.device)
+            feat = torch.empty(B, n_win, Z, Fd, device=xin.device, dtype=torch.float32)
+            n_terms = _TERMS.get(_HEAD_PRECISION)
+            if n_terms is None:
+                raise ValueError(f"FASTB200_HEAD_PRECISION={_HEAD_PRECISION!r}: expected one of {sorted(_TERMS)}")
+            if not need_grad and n_terms and lib.fastb200_head_tc_supported(desc):
+                # inference: tensor-core head (split-bf16 tcgen05 MMAs), nothing saved
+                packed = torch.empty(lib.fastb200_head_packed_tc_bytes(desc, n_terms), device=xin.device, dtype=torch.uint8)
+                N.check(lib.fastb200_head_pack_tc(desc, N.ptr(flat), N.ptr(packed), n_terms, st), "head_pack_tc")
+                N.check(lib.fastb200_head_fwd_tc(desc, N.ptr(packed), N.ptr(xin), B, T, n_win, step, N.ptr(feat), n_terms, st),
+                        "head_fwd_tc")
+                return feat
             packed = torch.empty(lib.fastb200_head_packed_floats(desc), device=xin.device, dtype=torch.float32)
             N.check(lib.fastb200_head_pack(desc, N.ptr(flat), N.ptr(packed), st), "head_pack")
-            feat = torch.empty(B, n_win, Z, Fd, device=xin.device, dtype=torch.float32)
             saved = None
             if need_grad:
                 saved = torch.empty(lib.fastb200_head_saved_floats(desc, B, n_win), device=xin.device, dtype=torch.float32)

@@ -116,6 +116,22 @@ int fastb200_head_bwd(const fastb200_model* m, const float* packed, const float*
 int fastb200_head_unpack_grad(const fastb200_model* m, const float* params, const float* gpacked,
                               float* grads, void* stream);
 
+/* ---- zone embedding head on the tensor cores (tcgen05 / TMEM), inference forward ------------------------------ */
+/*
+ * Same function as fastb200_head_fwd with saved == NULL (FAST.forward_head, fast.py:242-252, under no_grad), computed
+ * by bf16 tensor-core MMAs with fp32 accumulation and split operands: every fp32 operand is the sum of n_terms bf16
+ * terms (n_terms = 3: 24 mantissa bits, fp32-equivalent; n_terms = 2: 16 bits, still ~1e-6 on the features because
+ * the feature is a 246-sample mean).  Shapes supported: dim_cnn == 32, 132 <= window_len <= 252, zones of <= 16
+ * electrodes -- fastb200_head_tc_supported() returns 1 for them; the FFMA kernel above covers the rest.
+ */
+int     fastb200_head_tc_supported(const fastb200_model* m);
+int64_t fastb200_head_packed_tc_bytes(const fastb200_model* m, int n_terms);
+/* Collapses cnn1 o cnn2, splits every head weight into n_terms bf16 terms and lays them out as K-major UMMA operands. */
+int fastb200_head_pack_tc(const fastb200_model* m, const float* params, void* packed, int n_terms, void* stream);
+/*   packed: output of fastb200_head_pack_tc with the same n_terms.   x (B, C, T)   feat (B, n_win, Z, F) */
+int fastb200_head_fwd_tc(const fastb200_model* m, const void* packed, const float* x, int B, int T, int n_win,
+                         int step, float* feat, int n_terms, void* stream);
+
 /* ---- transformer (input_layer, CLS, pos, L x AttentionBlock, last_layer) --------------------------------- */
 /* Floats saved per forward for the backward: B * (n_layers + 1) * n_tok * D  (block inputs + final tokens). */
 int64_t fastb200_transformer_saved_floats(const fastb200_model* m, int B, int n_win);
