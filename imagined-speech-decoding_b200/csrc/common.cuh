@@ -88,6 +88,9 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
+#ifndef FB_MBAR_SUSPEND_NS
+#define FB_MBAR_SUSPEND_NS 500u
+#endif
 // Bounded wait: a byte-count mistake must surface as a trap (launch error), never as a hung GPU box.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     uint32_t done = 0;
@@ -97,7 +100,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         asm volatile("{\n\t.reg .pred p;\n\t"
                      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
                      "selp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(done) : "r"(smem_u32(bar)), "r"(parity), "r"(20000u) : "memory");
+                     : "=r"(done) : "r"(smem_u32(bar)), "r"(parity), "r"(FB_MBAR_SUSPEND_NS) : "memory");
         if (done) return;
     }
     __trap();

@@ -20,9 +20,10 @@
 //     by a bulk async copy); the 148 CTAs are apportioned to zones by cost so every zone walks the trial list at the
 //     same rate and the 8 zone passes over a trial hit L2, not HBM.
 //
-// Warp roles (640 threads): warps 0-7 / 8-15 epilogue of stream A / B (TMEM lane quadrant = warp % 4, column half =
-// (warp / 4) % 2), warp 16 MMA issuer (one elected thread) and TMEM allocator, warps 17-19 electrode loaders (fused
-// unfold + zone gather + split).
+// Warp roles (768 threads): warps 0-7 / 8-15 epilogue of stream A / B (TMEM lane quadrant = warp % 4, column half =
+// (warp / 4) % 2), warps 16 / 17 MMA issuer of stream A / B (one elected lane each; while one issuer sits in a barrier
+// wait the other keeps the tensor pipe fed), warps 18 / 19 electrode copier of stream A / B
+// (fused unfold + zone gather, cp.async ring), warps 20-23 converters (staged fp32 -> split-bf16 operand tile).
 #include "common.cuh"
 #include <cuda_bf16.h>
 #include <stdlib.h>
@@ -33,9 +34,12 @@ namespace tc {
 constexpr int F = 32;                   // dim_cnn handled by this kernel
 constexpr int RY = 132;                 // rows of a conv operand tile: 2 zero rows + 128 + 2 zero rows
 constexpr int RX = 136;                 // rows of an electrode tile: 128 + 4 taps + 1 (tap-pair trick) + spare
-constexpr int EPI_WARPS = 16, MMA_WARP = 16, LOAD_WARP0 = 17, LOAD_WARPS = 3;   // 20 warps = 5 per SM sub-partition -> 96 registers per thread
+constexpr int EPI_WARPS = 16, MMA_WARP = 16, MMA_WARPS = 2, COPY_WARP0 = 18, CONV_WARP0 = 20, LOAD_WARPS = 6;
+// 24 warps launch with 80 registers each; the four epilogue warpgroups then grow to EPI_REGS and the two service
+// warpgroups (issuers + copiers, converters) shrink to SVC_REGS (setmaxnreg): the CTA register pool is what it launched with.
+constexpr int EPI_REGS = 96, SVC_REGS = 48;      // pool = 768 x 80: 16 warps x (96 - 80) == 8 warps x (80 - 48)
 constexpr int CW = 16;                  // accumulator columns per epilogue warp (two warps share a TMEM lane quadrant)
-constexpr int THREADS = (EPI_WARPS + 1 + LOAD_WARPS) * 32;
+constexpr int THREADS = (EPI_WARPS + MMA_WARPS + LOAD_WARPS) * 32;
 constexpr int EMB_CHUNKS = 10;          // K chunks (8 bf16) of the collapsed embed filter: 5 taps x 16 electrodes
 constexpr int CONV_CHUNKS = 20;         // 5 taps x 32 channels / 8
 
@@ -233,11 +237,14 @@ struct FwdArgs {
 
 struct Smem {                                  // fixed part at the start of dynamic shared memory
     uint64_t w_full;
-    uint64_t x_full[2], x_empty[2], d_full[2], y_ready[2], d_free[2];
+    uint64_t x_full[2], x_empty[2], de_full[2], dm_full[2], ye_ready[2], yc_ready[2], d_free[2];
+    uint64_t stg_full[2][2], stg_empty[2][2];
     uint32_t tmem_base;
     int counter[2];
     float red[2][EPI_WARPS][CW];
 };
+constexpr int STG_BYTES = 16 * RX * 4;               // one staged electrode tile: raw fp32 [16 channels][RX rows]
+__host__ __device__ constexpr int stg_tiles(int NT) { return NT == 2 ? 2 : 1; }   // staging ring depth PER STREAM (shared-memory budget)
 constexpr int SMEM_HDR = 3072;                 // bytes reserved for Smem in front of the operand tiles
 static_assert(sizeof(Smem) <= SMEM_HDR, "Smem header overflows its reservation");
 
@@ -246,14 +253,17 @@ template <int NT, bool PROF>
 __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_constant__ FwdArgs a) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
-    uint8_t* wz = smem_raw + SMEM_HDR;                                  // this zone's split weights (zone_bytes(NT))
+    uint8_t* wz = smem_raw + SMEM_HDR;                              // this zone's split weights (zone_bytes(NT))
     uint8_t* xs = wz + zone_bytes(NT);                              // [2 streams] electrode tiles
-    uint8_t* ys = xs + 2 * x_bytes(NT);                             // [2 streams] conv operand tiles
+    uint8_t* ys = xs + 2 * x_bytes(NT);                             // [2 streams][2 item parities] conv operand tiles
     constexpr int LB = lb(NT);
+    constexpr int STG = stg_tiles(NT);
     constexpr int DCOLS = 32 * NT;                                  // accumulator columns per stream
-    constexpr int TMEM_COLS = 2 * DCOLS <= 128 ? 128 : 256;
+    constexpr int TMEM_COLS = 4 * DCOLS <= 256 ? 256 : 512;         // conv accumulators [0, 2 DCOLS), embed accumulators after
 
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    // warp index through a shuffle: tells the compiler it is warp-uniform, so role-dependent values (stream, descriptors)
+    // live in uniform registers -- the form UTCHMMA wants -- instead of being re-uniformised per MMA
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
     const int z = a.cta_zone[blockIdx.x];
     const int rank = a.cta_rank[blockIdx.x], nz = a.zone_ctas[z];
     const int BN = a.B * a.n_win;
@@ -264,16 +274,19 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
     if (tid == 0) {
         mbar_init(&sm.w_full, 1);
         for (int s = 0; s < 2; ++s) {
-            mbar_init(&sm.x_full[s], LOAD_WARPS * 32);
+            mbar_init(&sm.x_full[s], 64);
+            for (int i = 0; i < 2; ++i) { mbar_init(&sm.stg_full[s][i], 32); mbar_init(&sm.stg_empty[s][i], 64); }
             mbar_init(&sm.x_empty[s], 1);
-            mbar_init(&sm.d_full[s], 1);
-            mbar_init(&sm.y_ready[s], EPI_WARPS * 16);
+            mbar_init(&sm.de_full[s], 1);
+            mbar_init(&sm.dm_full[s], 1);
+            mbar_init(&sm.ye_ready[s], EPI_WARPS * 16);
+            mbar_init(&sm.yc_ready[s], EPI_WARPS * 16);
             mbar_init(&sm.d_free[s], EPI_WARPS * 16);
         }
         sm.counter[0] = sm.counter[1] = 0;
         fence_mbar_init();
     }
-    for (int i = tid; i < 2 * y_bytes(NT) / 16; i += THREADS) reinterpret_cast<uint4*>(ys)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < 4 * y_bytes(NT) / 16; i += THREADS) reinterpret_cast<uint4*>(ys)[i] = make_uint4(0, 0, 0, 0);
     if (warp == MMA_WARP) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)), "n"(TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -282,7 +295,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem = sm.tmem_base;
+    const uint32_t tmem = __shfl_sync(0xffffffffu, sm.tmem_base, 0);
     if (rank >= BN) {                                               // nothing to do for this CTA (tiny batches)
         __syncthreads();
         if (warp == MMA_WARP) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS) : "memory");
@@ -290,129 +303,165 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
     }
     const int n_it = (BN - rank + nz - 1) / nz;                     // items rank, rank + nz, ...
 
-    if (warp == MMA_WARP) {
-        // =========================================== MMA issuer ===========================================
-        {
-            if (lane == 0) {
-                mbar_expect_tx(&sm.w_full, (uint32_t)zone_bytes(NT));
-                bulk_g2s(wz, a.packed + (size_t)z * zone_bytes(NT), (uint32_t)zone_bytes(NT), &sm.w_full);
-            }
-            __syncwarp();
-            mbar_wait(&sm.w_full, 0);
-            const uint32_t w_emb = smem_u32(wz), w_c3 = w_emb + EMB_CHUNKS * LB, w_c4 = w_c3 + CONV_CHUNKS * LB;
-            long long pw[4] = {0, 0, 0, 0};
-            const long long t_start = PROF ? clock64() : 0;
-            for (int it = 0; it < n_it; ++it) {
-                // collapsed cnn1 o cnn2 on the electrode tiles
-                for (int s = 0; s < 2; ++s) {
-                    long long c0 = 0, c1 = 0;
-                    if (PROF) c0 = clock64();
-                    mbar_wait(&sm.x_full[s], it & 1);
-                    if (PROF) { c1 = clock64(); pw[0] += c1 - c0; }
-                    if (it > 0) mbar_wait(&sm.d_free[s], (it - 1) & 1);
-                    if (PROF) pw[1] += clock64() - c1;
-                    tc_fence_after();
-                    const uint32_t d = tmem + s * DCOLS;
-                    const uint32_t xb = smem_u32(xs) + s * x_bytes(NT);
-                    uint32_t acc = 0;
-                    if (n_xchunk == 2) {
-#pragma unroll
-                        for (int k = 0; k < TAPS; ++k)
-#pragma unroll
-                            for (int t = 0; t < NT; ++t) {
-                                umma(d, desc_lo(xb + t * (2 * RX * 16) + k * 16, RX * 16), desc_lo(w_emb + 2 * k * LB, LB),
-                                     idesc_bf16(32 * (NT - t)), acc);
-                                acc = 1;
-                            }
-                    } else {                                        // 8 electrodes: one K16 step = taps (2p, 2p+1), LBO = one row
-#pragma unroll
-                        for (int p = 0; p < 3; ++p)
-#pragma unroll
-                            for (int t = 0; t < NT; ++t) {
-                                umma(d, desc_lo(xb + t * (2 * RX * 16) + 2 * p * 16, 16), desc_lo(w_emb + 2 * p * LB, LB),
-                                     idesc_bf16(32 * (NT - t)), acc);
-                                acc = 1;
-                            }
-                    }
-                    umma_commit(&sm.d_full[s]);
-                    umma_commit(&sm.x_empty[s]);
-                }
-                // cnn3, cnn4 on the conv operand tiles
-                for (int layer = 0; layer < 2; ++layer) {
-                    const uint32_t wl = layer == 0 ? w_c3 : w_c4;
-                    for (int s = 0; s < 2; ++s) {
-                        long long c0 = 0;
-                        if (PROF) c0 = clock64();
-                        mbar_wait(&sm.y_ready[s], layer);           // two completions per item: phase = layer
-                        if (PROF) pw[2 + layer] += clock64() - c0;
-                        tc_fence_after();
-                        const uint32_t d = tmem + s * DCOLS;
-                        const uint32_t yb = smem_u32(ys) + s * y_bytes(NT);
-                        uint32_t acc = 0;
-#pragma unroll
-                        for (int k = 0; k < TAPS; ++k)
-#pragma unroll
-                            for (int h = 0; h < 2; ++h)
-#pragma unroll
-                                for (int t = 0; t < NT; ++t) {
-                                    umma(d, desc_lo(yb + t * (4 * RY * 16) + 2 * h * (RY * 16) + k * 16, RY * 16),
-                                         desc_lo(wl + (4 * k + 2 * h) * LB, LB), idesc_bf16(32 * (NT - t)), acc);
-                                    acc = 1;
-                                }
-                        umma_commit(&sm.d_full[s]);
-                    }
-                }
-            }
-            if (PROF && lane == 0) {
-                long long* o = a.prof + (size_t)blockIdx.x * 16;
-                o[0] = clock64() - t_start; o[1] = pw[0]; o[2] = pw[1]; o[3] = pw[2]; o[4] = pw[3]; o[5] = n_it;
-            }
+    if (warp < EPI_WARPS) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(EPI_REGS));
+    else asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(SVC_REGS));
+
+    if (warp >= MMA_WARP && warp < MMA_WARP + MMA_WARPS) {
+        // ===================================== MMA issuer of stream s = warp - 16 =====================================
+        // Software pipeline across items (per stream s):   ... C3(i) | E(i+1) | C4(i) | C3(i+1) ...
+        // The embed of the NEXT item is issued between cnn3 and cnn4 of the current one (own accumulator, operand tiles
+        // double-buffered by item parity), so every epilogue has at least one full conv stage of the other stream to
+        // hide behind and the tensor pipe never waits for the short embed stage's epilogue.
+        const int s = warp - MMA_WARP;
+        if (s == 0 && lane == 0) {
+            mbar_expect_tx(&sm.w_full, (uint32_t)zone_bytes(NT));
+            bulk_g2s(wz, a.packed + (size_t)z * zone_bytes(NT), (uint32_t)zone_bytes(NT), &sm.w_full);
         }
-    } else if (warp >= LOAD_WARP0) {
-        // ============================ electrode loaders: unfold + zone gather + split ============================
-        // Thread slot k of a stream handles tile entry i = lt + k * 96 = (electrode chunk j, row r): the same (j, r) for
-        // every item, so the eight gather offsets chan[c] * T + t are computed once, outside the item loop.
-        const int lt = tid - LOAD_WARP0 * 32;
-        const int* chan = a.chan + a.zoff[z];
-        constexpr int NLT = LOAD_WARPS * 32;
-        constexpr int SLOTS = (2 * RX + NLT - 1) / NLT;             // 3 for two electrode chunks
-        for (int it = 0; it < n_it; ++it) {
-            const int item = rank + it * nz;
-            const int b = item / a.n_win, n = item - b * a.n_win;
-            const float* xb = a.x + (size_t)b * a.C * a.T + (size_t)n * a.step;
-            for (int s = 0; s < 2; ++s) {
-                if (it > 0) mbar_wait(&sm.x_empty[s], (it - 1) & 1);
-                const int tb = s == 0 ? 0 : a.tb1;
-                uint8_t* xt = xs + s * x_bytes(NT);
-                if (!(PROF && (a.dbg & 4))) {
-                    float v[SLOTS][8];
+        __syncwarp();
+        mbar_wait(&sm.w_full, 0);
+        const uint32_t w_emb = smem_u32(wz), w_c3 = w_emb + EMB_CHUNKS * LB, w_c4 = w_c3 + CONV_CHUNKS * LB;
+        long long pw[4] = {0, 0, 0, 0};
+        const long long t_start = PROF ? clock64() : 0;
+
+        auto issue_embed = [&](int it) {                     // collapsed cnn1 o cnn2 on the electrode tile
+            long long c0 = 0;
+            if (PROF) c0 = clock64();
+            mbar_wait(&sm.x_full[s], it & 1);
+            if (PROF) pw[0] += clock64() - c0;
+            tc_fence_after();
+            const uint32_t d = tmem + (2 + s) * DCOLS;
+            // descriptors = one base per operand + compile-time offsets in 16-byte units (keeps the issuer's live state tiny)
+            const uint32_t xb = smem_u32(xs) + s * x_bytes(NT);
+            const uint32_t wd = desc_lo(w_emb, LB);
+            uint32_t acc = 0;
+            if (n_xchunk == 2) {
+                const uint32_t xd = desc_lo(xb, RX * 16);
 #pragma unroll
-                    for (int k = 0; k < SLOTS; ++k) {               // all loads of this tile in flight before the first use
-                        const int i = lt + k * NLT;
-                        const int j = i >= RX ? 1 : 0, r = i - j * RX;
-                        const int t = tb + r;
-                        const bool row_ok = i < n_xchunk * RX && t < a.W;
+                for (int k = 0; k < TAPS; ++k)
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            const int c = 8 * j + e;
-                            v[k][e] = (row_ok && c < Cz) ? __ldg(xb + (size_t)chan[c] * a.T + t) : 0.f;
-                        }
+                    for (int t = 0; t < NT; ++t) {
+                        umma(d, xd + (t * (2 * RX * 16) + k * 16) / 16, wd + (2 * k * LB) / 16, idesc_bf16(32 * (NT - t)), acc);
+                        acc = 1;
                     }
+            } else {                                                // 8 electrodes: one K16 step = taps (2p, 2p+1), LBO = one row
+                const uint32_t xd = desc_lo(xb, 16);
 #pragma unroll
-                    for (int k = 0; k < SLOTS; ++k) {
-                        const int i = lt + k * NLT;
-                        const int j = i >= RX ? 1 : 0, r = i - j * RX;
-                        if (i < n_xchunk * RX) {
-                            uint4 o[NT];
-                            split8<NT>(v[k], o);
+                for (int p = 0; p < 3; ++p)
 #pragma unroll
-                            for (int tm = 0; tm < NT; ++tm)
-                                *reinterpret_cast<uint4*>(xt + tm * (2 * RX * 16) + j * (RX * 16) + r * 16) = o[tm];
+                    for (int t = 0; t < NT; ++t) {
+                        umma(d, xd + (t * (2 * RX * 16) + 2 * p * 16) / 16, wd + (2 * p * LB) / 16, idesc_bf16(32 * (NT - t)), acc);
+                        acc = 1;
+                    }
+            }
+            umma_commit(&sm.de_full[s]);
+            umma_commit(&sm.x_empty[s]);
+        };
+        auto issue_conv = [&](int layer, int it) {           // cnn3 (layer 0) / cnn4 (layer 1) on the conv operand tile
+            long long c0 = 0, c1 = 0;
+            if (PROF) c0 = clock64();
+            if (layer == 0) {
+                mbar_wait(&sm.ye_ready[s], it & 1);
+                if (PROF) { c1 = clock64(); pw[2] += c1 - c0; }
+                if (it > 0) mbar_wait(&sm.d_free[s], (it - 1) & 1);  // GELU epilogue of the previous item drained D
+                if (PROF) pw[1] += clock64() - c1;
+            } else {
+                mbar_wait(&sm.yc_ready[s], it & 1);
+                if (PROF) pw[3] += clock64() - c0;
+            }
+            tc_fence_after();
+            const uint32_t wl = layer == 0 ? w_c3 : w_c4;
+            const uint32_t d = tmem + s * DCOLS;
+            const uint32_t yd = desc_lo(smem_u32(ys) + (2 * s + (it & 1)) * y_bytes(NT), RY * 16);
+            const uint32_t wd = desc_lo(wl, LB);
+            uint32_t acc = 0;
+#pragma unroll
+            for (int k = 0; k < TAPS; ++k)
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+#pragma unroll
+                    for (int t = 0; t < NT; ++t) {
+                        umma(d, yd + (t * (4 * RY * 16) + 2 * h * (RY * 16) + k * 16) / 16, wd + ((4 * k + 2 * h) * LB) / 16,
+                             idesc_bf16(32 * (NT - t)), acc);
+                        acc = 1;
+                    }
+            umma_commit(&sm.dm_full[s]);
+        };
+        issue_embed(0);
+        for (int it = 0; it < n_it; ++it) {
+            issue_conv(0, it);
+            if (it + 1 < n_it) issue_embed(it + 1);
+            issue_conv(1, it);
+        }
+        if (PROF && lane == 0 && s == 0) {
+            long long* o = a.prof + (size_t)blockIdx.x * 16;
+            o[0] = clock64() - t_start; o[1] = pw[0]; o[2] = pw[1]; o[3] = pw[2]; o[4] = pw[3]; o[5] = n_it;
+        }
+    } else if (warp >= COPY_WARP0) {
+        // ============================ electrode loaders: unfold + zone gather + split ============================
+        // Copier warp of stream s (warps 18, 19) streams item after item of its stream's electrode tile global -> shared
+        // staging with 4-byte cp.async (no alignment requirement on the trial rows; zero fill outside the zone / window),
+        // a ring of STG tiles deep, so the global latency costs neither registers nor issue slots.  Two converter warps
+        // per stream (warps 20-23) turn a landed tile into the split-bf16 K-major operand tile.  Copy and conversion are
+        // different warps because the fence.proxy.async after the converter's stores would otherwise wait for the
+        // copier's in-flight prefetches and serialise them.
+        const int* chan = a.chan + a.zoff[z];
+        const int n_ch = 8 * n_xchunk;
+        if (warp < CONV_WARP0) {
+            const int s = warp - COPY_WARP0;
+            const uint32_t stg_u32 = smem_u32(ys + 4 * y_bytes(NT)) + s * STG * STG_BYTES;
+            const int tb = s == 0 ? 0 : a.tb1;
+#pragma unroll 1
+            for (int it = 0; it < n_it; ++it) {
+                const int slot = it % STG;
+                if (it >= STG) mbar_wait(&sm.stg_empty[s][slot], ((it / STG) - 1) & 1);
+                const int item = rank + it * nz;
+                const int b = item / a.n_win, n = item - b * a.n_win;
+                const float* xb = a.x + (size_t)b * a.C * a.T + (size_t)n * a.step + tb + lane;
+                const uint32_t dst0 = stg_u32 + slot * STG_BYTES + lane * 4;
+#pragma unroll 1
+                for (int c = 0; c < n_ch; ++c) {
+                    const float* p = xb + (size_t)chan[min(c, Cz - 1)] * a.T;
+                    const bool ch_ok = c < Cz;
+#pragma unroll
+                    for (int k = 0; k < (RX + 31) / 32; ++k) {
+                        const int r = lane + 32 * k;
+                        if (r < RX) {
+                            const uint32_t nbytes = (ch_ok && tb + r < a.W) ? 4u : 0u;
+                            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst0 + (c * RX + 32 * k) * 4),
+                                         "l"(nbytes ? p + 32 * k : a.x), "r"(nbytes) : "memory");
                         }
                     }
                 }
+                asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(&sm.stg_full[s][slot])) : "memory");
+            }
+            asm volatile("cp.async.wait_all;" ::: "memory");
+        } else {
+            const int s = (warp - CONV_WARP0) >> 1, half = (warp - CONV_WARP0) & 1;
+            const float* stg = reinterpret_cast<const float*>(ys + 4 * y_bytes(NT)) + s * STG * (STG_BYTES / 4);
+            uint8_t* xt = xs + s * x_bytes(NT);
+#pragma unroll 1
+            for (int it = 0; it < n_it; ++it) {
+                const int slot = it % STG;
+                mbar_wait(&sm.stg_full[s][slot], (it / STG) & 1);
+                if (it > 0) mbar_wait(&sm.x_empty[s], (it - 1) & 1);
+                const float* sg = stg + slot * (STG_BYTES / 4);
+                for (int j = 0; j < n_xchunk; ++j)
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) {
+                        const int r = lane + 32 * (2 * k + half);
+                        if (r < RX) {
+                            float v[8];
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) v[e] = sg[(8 * j + e) * RX + r];
+                            uint4 o[NT];
+                            split8<NT>(v, o);
+#pragma unroll
+                            for (int tm = 0; tm < NT; ++tm) *reinterpret_cast<uint4*>(xt + tm * (2 * RX * 16) + j * (RX * 16) + r * 16) = o[tm];
+                        }
+                    }
                 fence_proxy_async();
                 mbar_arrive(&sm.x_full[s]);
+                mbar_arrive(&sm.stg_empty[s][slot]);
             }
         }
     } else {
@@ -420,105 +469,131 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
         const int s = warp >> 3, h = (warp >> 2) & 1, q = warp & 3;
         const int m = 32 * q + lane;                                // accumulator row = TMEM lane
         const int t = (s == 0 ? 0 : a.tb1) + m;                     // time sample of this row
-        const uint32_t d_addr = tmem + ((uint32_t)(32 * q) << 16) + s * DCOLS + CW * h;
-        uint8_t* yt = ys + s * y_bytes(NT) + (m + 2) * 16 + 2 * h * (RY * 16);
+        const uint32_t lane_addr = tmem + ((uint32_t)(32 * q) << 16) + CW * h;
+        uint8_t* yt0 = ys + 2 * s * y_bytes(NT) + (m + 2) * 16 + 2 * h * (RY * 16);
         const float* beff = reinterpret_cast<const float*>(wz + (EMB_CHUNKS + 2 * CONV_CHUNKS) * LB) + CW * h;
         const bool live = t < a.T_out;                              // rows past the window are the next conv's zero padding
         const bool own = live && (s == 0 ? t < a.split : t >= a.split);
         mbar_wait(&sm.w_full, 0);                                   // beff visible
         long long ew = 0, ep[5] = {0, 0, 0, 0, 0};
-        for (int it = 0; it < n_it; ++it) {
-            for (int stage = 0; stage < 3; ++stage) {
-                long long c0 = 0;
-                if (PROF) c0 = clock64();
-                mbar_wait(&sm.d_full[s], (it + stage) & 1);         // three completions per item
-                if (PROF) ew += clock64() - c0;
-                tc_fence_after();
-                float v[CW];
-                {
-                    float u[NT - 1][CW];
-                    tmem_ld16(d_addr, v);
+
+        // accumulator (NT column groups) -> v[CW]
+        auto drain = [&](uint32_t d_addr, float (&v)[CW]) {
+            float u[NT - 1][CW];
+            tmem_ld16(d_addr, v);
 #pragma unroll
-                    for (int tm = 1; tm < NT; ++tm) tmem_ld16(d_addr + 32 * tm, u[tm - 1]);
-                    tmem_ld_wait();
+            for (int tm = 1; tm < NT; ++tm) tmem_ld16(d_addr + 32 * tm, u[tm - 1]);
+            tmem_ld_wait();
 #pragma unroll
-                    for (int tm = 1; tm < NT; ++tm)
+            for (int tm = 1; tm < NT; ++tm)
 #pragma unroll
-                        for (int i = 0; i < CW; ++i) v[i] += u[tm - 1][i];
+                for (int i = 0; i < CW; i += 2) {
+                    const f32x2 sum = add2(pk(v[i], v[i + 1]), pk(u[tm - 1][i], u[tm - 1][i + 1]));
+                    unpk(sum, v[i], v[i + 1]);
                 }
-                long long c1 = 0;
-                if (PROF) { c1 = clock64(); ep[0] += c1 - c0; }       // includes the d_full wait (subtract ew)
-                if (stage < 2) {
-                    if (!(PROF && (a.dbg & 1)))
+        };
+        // v (+ bias) -> masked -> bf16 terms -> this item's operand tile; signals `ready`
+        auto to_operand = [&](float (&v)[CW], bool add_bias, int it, uint64_t* ready) {
+            uint8_t* yt = yt0 + (it & 1) * y_bytes(NT);
+            if (!(PROF && (a.dbg & 1)))
 #pragma unroll
-                    for (int j = 0; j < CW / 8; ++j) {
-                        float x8[8];
+            for (int j = 0; j < CW / 8; ++j) {
+                float x8[8];
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            float val = v[8 * j + e];
-                            if (stage == 0) val += beff[8 * j + e];
-                            x8[e] = live ? val : 0.f;
-                        }
-                        uint4 o[NT];
-                        split8<NT>(x8, o);
+                for (int e = 0; e < 8; ++e) {
+                    float val = v[8 * j + e];
+                    if (add_bias) val += beff[8 * j + e];
+                    x8[e] = live ? val : 0.f;
+                }
+                uint4 o[NT];
+                split8<NT>(x8, o);
 #pragma unroll
-                        for (int tm = 0; tm < NT; ++tm) *reinterpret_cast<uint4*>(yt + tm * (4 * RY * 16) + j * (RY * 16)) = o[tm];
-                    }
-                    long long c2 = 0;
-                    if (PROF) { c2 = clock64(); ep[1] += c2 - c1; }
-                    fence_proxy_async();
-                    if (PROF) ep[2] += clock64() - c2;
-                    tc_fence_before();
-                    mbar_arrive(&sm.y_ready[s]);
-                } else {
-                    tc_fence_before();
-                    mbar_arrive(&sm.d_free[s]);                     // accumulator drained: next item's embed may overwrite it
+                for (int tm = 0; tm < NT; ++tm) *reinterpret_cast<uint4*>(yt + tm * (4 * RY * 16) + j * (RY * 16)) = o[tm];
+            }
+            fence_proxy_async();
+            tc_fence_before();
+            mbar_arrive(ready);
+        };
+        auto epi_embed = [&](int it) {
+            long long c0 = 0;
+            if (PROF) c0 = clock64();
+            mbar_wait(&sm.de_full[s], it & 1);
+            if (PROF) ew += clock64() - c0;
+            tc_fence_after();
+            float v[CW];
+            drain(lane_addr + (2 + s) * DCOLS, v);
+            to_operand(v, true, it, &sm.ye_ready[s]);
+            if (PROF) ep[0] += clock64() - c0;
+        };
+        auto epi_cnn3 = [&](int it) {
+            long long c0 = 0;
+            if (PROF) c0 = clock64();
+            mbar_wait(&sm.dm_full[s], 0);                           // two completions per item: cnn3 = even, cnn4 = odd
+            if (PROF) ew += clock64() - c0;
+            tc_fence_after();
+            float v[CW];
+            drain(lane_addr + s * DCOLS, v);
+            to_operand(v, false, it, &sm.yc_ready[s]);
+            if (PROF) ep[1] += clock64() - c0;
+        };
+        auto epi_cnn4 = [&](int it) {
+            long long c0 = 0, c1 = 0;
+            if (PROF) c0 = clock64();
+            mbar_wait(&sm.dm_full[s], 1);
+            if (PROF) { c1 = clock64(); ew += c1 - c0; }
+            tc_fence_after();
+            float v[CW];
+            drain(lane_addr + s * DCOLS, v);
+            tc_fence_before();
+            mbar_arrive(&sm.d_free[s]);                             // accumulator drained: next item's cnn3 may overwrite it
 #pragma unroll
-                    for (int i = 0; i < CW; i += 2) {
-                        v[i] = own ? v[i] : 0.f;                    // gelu(0) == 0: rows this stream does not own add nothing
-                        v[i + 1] = own ? v[i + 1] : 0.f;
-                        if (!(PROF && (a.dbg & 2))) gelu2(v[i], v[i + 1]);
-                    }
-                    // sum over the warp's 32 rows by recursive halving (16 shuffles): lanes 2c, 2c+1 end up with column c
+            for (int i = 0; i < CW; i += 2) {
+                v[i] = own ? v[i] : 0.f;                            // gelu(0) == 0: rows this stream does not own add nothing
+                v[i + 1] = own ? v[i + 1] : 0.f;
+                if (!(PROF && (a.dbg & 2))) gelu2(v[i], v[i + 1]);
+            }
+            // sum over the warp's 32 rows by recursive halving (16 shuffles): lanes 2c, 2c+1 end up with column c
 #pragma unroll
-                    for (int st = 16; st >= 2; st >>= 1) {
-                        const bool upper = (lane & st) != 0;
+            for (int st = 16; st >= 2; st >>= 1) {
+                const bool upper = (lane & st) != 0;
 #pragma unroll
-                        for (int i = 0; i < st / 2; ++i) {
-                            const float keep = upper ? v[i + st / 2] : v[i];
-                            const float send = upper ? v[i] : v[i + st / 2];
-                            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, st);
-                        }
-                    }
-                    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
-                    long long c3 = 0;
-                    if (PROF) { c3 = clock64(); ep[3] += c3 - c1; }
-                    const int par = it & 1;
-                    if ((lane & 1) == 0) sm.red[par][warp][lane >> 1] = v[0];
-                    __syncwarp();
-                    int old = 0;
-                    if (lane == 0) {
-                        __threadfence_block();
-                        old = atomicAdd(&sm.counter[par], 1);
-                    }
-                    old = __shfl_sync(0xffffffffu, old, 0);
-                    if (old == EPI_WARPS - 1) {                     // last of the 16 warps: fixed-order sum -> deterministic
-                        __threadfence_block();
-                        float tot = 0.f;                            // lane = output channel co = 16 h' + c
-#pragma unroll
-                        for (int ss = 0; ss < 2; ++ss)
-#pragma unroll
-                            for (int qq = 0; qq < 4; ++qq) tot += sm.red[par][ss * 8 + (lane >> 4) * 4 + qq][lane & 15];
-                        const int item = rank + it * nz;
-                        a.feat[((size_t)item * a.Z + z) * F + lane] = tot / (float)a.T_out;
-                        __syncwarp();
-                        if (lane == 0) sm.counter[par] = 0;
-                    }
-                    if (PROF) ep[4] += clock64() - c3;
+                for (int i = 0; i < st / 2; ++i) {
+                    const float keep = upper ? v[i + st / 2] : v[i];
+                    const float send = upper ? v[i] : v[i + st / 2];
+                    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, st);
                 }
             }
+            v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+            const int par = it & 1;
+            if ((lane & 1) == 0) sm.red[par][warp][lane >> 1] = v[0];
+            __syncwarp();
+            int old = 0;
+            if (lane == 0) {
+                __threadfence_block();
+                old = atomicAdd(&sm.counter[par], 1);
+            }
+            old = __shfl_sync(0xffffffffu, old, 0);
+            if (old == EPI_WARPS - 1) {                             // last of the 16 warps: fixed-order sum -> deterministic
+                __threadfence_block();
+                float tot = 0.f;                                    // lane = output channel co = 16 h' + c
+#pragma unroll
+                for (int ss = 0; ss < 2; ++ss)
+#pragma unroll
+                    for (int qq = 0; qq < 4; ++qq) tot += sm.red[par][ss * 8 + (lane >> 4) * 4 + qq][lane & 15];
+                const int item = rank + it * nz;
+                a.feat[((size_t)item * a.Z + z) * F + lane] = tot / (float)a.T_out;
+                __syncwarp();
+                if (lane == 0) sm.counter[par] = 0;
+            }
+            if (PROF) ep[2] += clock64() - c1;
+        };
+        epi_embed(0);
+        for (int it = 0; it < n_it; ++it) {
+            epi_cnn3(it);
+            if (it + 1 < n_it) epi_embed(it + 1);
+            epi_cnn4(it);
         }
-        if (PROF && tid == 0) { long long* o = a.prof + (size_t)blockIdx.x * 16; o[6] = ew; o[8] = ep[0]; o[9] = ep[1]; o[10] = ep[2]; o[11] = ep[3]; o[12] = ep[4]; }
+        if (PROF && tid == 0) { long long* o = a.prof + (size_t)blockIdx.x * 16; o[6] = ew; o[8] = ep[0]; o[9] = ep[1]; o[10] = ep[2]; }
         if (PROF && tid == 256) a.prof[(size_t)blockIdx.x * 16 + 7] = ew;
     }
     tc_fence_before();
@@ -607,7 +682,8 @@ extern "C" int fastb200_head_fwd_tc(const fastb200_model* m, const void* packed,
         for (int z = 0; z < Z && c < grid; ++z)
             if (given[z] < n_cta[z]) { a.cta_zone[c] = (uint8_t)z; a.cta_rank[c] = (uint8_t)given[z]++; ++c; }
     for (int z = 0; z < Z; ++z) a.zone_ctas[z] = (uint8_t)n_cta[z];
-    const size_t smem = tc::SMEM_HDR + tc::zone_bytes(n_terms) + 2 * tc::x_bytes(n_terms) + 2 * tc::y_bytes(n_terms);
+    const size_t smem = tc::SMEM_HDR + tc::zone_bytes(n_terms) + 2 * tc::x_bytes(n_terms) + 4 * tc::y_bytes(n_terms) +
+                        2 * tc::stg_tiles(n_terms) * tc::STG_BYTES;
     cudaError_t e;
 #define LAUNCH_TC(NTT, PROFF)                                                                                      \
     e = cudaFuncSetAttribute(tc::head_fwd_tc_kernel<NTT, PROFF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \

@@ -56,7 +56,7 @@ from fast import _native as N
 lib = N.lib()
 lib.fastb200_debug_set_tc_profile.argtypes = [ctypes.c_void_p]
 lib.fastb200_debug_set_tc_profile.restype = None
-for mode, dbg in (("bf16x3", 0), ("bf16x2", 0), ("bf16x2", 1), ("bf16x2", 2), ("bf16x2", 4), ("bf16x2", 7)):
+for mode, dbg in (("bf16x3", 0), ("bf16x2", 0), ("bf16x2", 7)):
     os.environ["FASTB200_TC_DBG"] = str(dbg)
     FM.set_head_precision(mode)
     prof = torch.zeros(148, 16, dtype=torch.int64, device="cuda")
@@ -68,6 +68,6 @@ for mode, dbg in (("bf16x3", 0), ("bf16x2", 0), ("bf16x2", 1), ("bf16x2", 2), ("
     p = prof.double().cpu()
     n_it = p[:, 5]
     names = ["mma total", "wait x_full", "wait d_free", "wait y_ready(E epi)", "wait y_ready(C3 epi)", "items", "epiA wait d_full", "epiB wait d_full",
-             "epi wait+tmem_ld (3 stages)", "epi split+STS (2 stages)", "epi fence.proxy (2)", "epi gelu+reduce", "epi red/atomic/feat"]
+             "epi embed (incl wait)", "epi cnn3 (incl wait)", "epi cnn4 after wait"]
     print(mode, "dbg", dbg, "per-item cycles (mean over CTAs):", {n: round(float((p[:, i] / n_it).mean()), 1) for i, n in enumerate(names) if i != 5},
           "items/CTA", float(n_it.mean()), "max total Mcyc", float(p[:, 0].max()) / 1e6, flush=True)
