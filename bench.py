@@ -8,8 +8,9 @@ steps cannot serve each other from cache.  One "step" = the whole hot path over 
 + 8 x Conv4Layers (one kernel), input layer + CLS/pos + 4 transformer blocks + classifier (one kernel), argmax.
 
   value   trials/s, input already resident in HBM, K steps timed with CUDA events, max over ranks
-  e2e     trials/s through the public drop-in API (``model(x)`` as ``inference_on_loader`` calls it) with the batch in
-          pinned HOST memory: H2D copy, kernels and the D2H read of the predictions all inside the timed region
+  e2e     trials/s through the public drop-in API (``model.predict(x_host)``: the argmax-of-logits op of
+          ``inference_on_loader``) with the batch in pinned HOST memory: the chunked H2D copy (overlapped with the kernels
+          on a side stream), the kernels and the D2H read of the predictions are all inside the timed region
   extra   training throughput (FusedTrainer, fwd+bwd+AdamW) and a small batch sweep, outside the headline
 
 Multi-GPU (torchrun): trials are independent, so ranks shard them with NO data-path collective (weak scaling: every
@@ -41,6 +42,15 @@ import torch
 FLOP_INFER_DIRECT = 388_426_048
 HEAD_MAC_DIRECT_PER_WINDOW = 38_793_216
 HEAD_MAC_EXEC_PER_WINDOW = 246 * 32 * 5 * 64 + 8 * 2 * 246 * 32 * 160       # collapsed embed (sum Cz = 64) + 8 zones x (cnn3 + cnn4)
+# tensor-core head: MMA flops actually issued per window (M = 128 rows x 2 streams; per K16 step one MMA per activation
+# term with N = 32 * (terms - i); embed: 3 K16 steps for zones of <= 8 electrodes, 5 otherwise; cnn3 / cnn4: 10 each)
+PROD_ZONE_SIZES = (6, 9, 6, 7, 7, 10, 15, 4)
+
+
+def tc_mma_flop_per_window(n_terms):
+    n_sum = sum(32 * (n_terms - i) for i in range(n_terms))
+    steps = sum((3 if cz <= 8 else 5) + 20 for cz in PROD_ZONE_SIZES)
+    return 2 * steps * 2.0 * 128 * 16 * n_sum
 FLOP_TRAIN_DIRECT = 1_140_087_744
 BYTES_PER_TRIAL = 64 * 795 * 4
 
@@ -157,6 +167,7 @@ def run_reference(args, rank):
 
 def workload_config(args):
     return {"workload": "FAST inference, BASELINE configs[1] (batch sweep top end)", "batch_per_gpu": args.batch, "channels": 64,
+            "head_precision": getattr(args, "head_precision", None),
             "samples": 795, "window_len": 250, "slide_step": 125, "zones": 8, "dim_cnn": 32, "dim_token": 32, "layers": 4,
             "heads": 8, "classes": 5, "l2_policy": "input per step (1.67 GB at batch 8192) larger than the 126 MB L2",
             "parallelism": f"trial-sharded x{args.gpus}, no data-path collective"}
@@ -174,7 +185,10 @@ def run_b200(args, rank, world, local_rank):
     from fast import _native as N
     from fast.models import FAST
     from fast.train import FusedTrainer
+    from fast.models import fast as FM
     N.lib()                                                                     # fail loudly if the extension is missing
+    FM.set_head_precision(args.head_precision)
+    n_terms = FM._TERMS[args.head_precision]
     B, K, W = args.batch, args.steps, args.warmup
     cfg = prod_cfg()
     torch.manual_seed(42)
@@ -224,8 +238,7 @@ def run_b200(args, rank, world, local_rank):
     ph = torch.empty(B, dtype=torch.int64, pin_memory=True)
 
     def e2e_step():
-        with torch.no_grad():
-            ph.copy_(model(xh.to(dev, non_blocking=True)).argmax(1), non_blocking=True)
+        ph.copy_(model.predict(xh, chunk=args.e2e_chunk), non_blocking=True)
 
     for _ in range(max(3, W // 2)):
         e2e_step()
@@ -249,41 +262,56 @@ def run_b200(args, rank, world, local_rank):
             dist.destroy_process_group()
         return
 
-    # ---- roofline of the dominant kernel (head_fwd: 99.9 % of the forward arithmetic)
+    # ---- roofline of the dominant kernel (the zone-embedding head: 99.9 % of the forward arithmetic)
     peaks = {}
     pk_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(pk_path):
         peaks = json.load(open(pk_path))
     n_win = 5
-    alg_flop = 2.0 * HEAD_MAC_DIRECT_PER_WINDOW * n_win * B
-    exe_flop = 2.0 * HEAD_MAC_EXEC_PER_WINDOW * n_win * B
-    fp32_peak = 148 * 128 * 2 * (peaks.get("sm_max_mhz", 1965.0) * 1e6) / 1e12     # FFMA lanes x 2 flop x clock
-    tensor_peak = peaks.get("bf16_tflops_sustained", 1400.0)
+    alg_flop = 2.0 * HEAD_MAC_DIRECT_PER_WINDOW * n_win * B                      # direct form, as the reference computes it
+    exe_flop = 2.0 * HEAD_MAC_EXEC_PER_WINDOW * n_win * B                        # fp32-equivalent flops after the exact collapse
     ach = alg_flop / (head_ms * 1e-3) / 1e12
     exe = exe_flop / (head_ms * 1e-3) / 1e12
-    roofline = {"kernel": "head_fwd_kernel<32>", "bound": "fp32-fma (CUDA-core kernel; see DESIGN.md section 6)", "achieved": ach,
-                "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak, "executed": exe, "frac_executed": exe / fp32_peak,
-                "frac_of_tensor_peak": ach / tensor_peak, "tensor_peak": tensor_peak,
-                "peak_source": "FP32 FMA pipe = 148 SM x 128 lanes x 2 x sm_max_mhz (MEASURED_PEAKS.json clock); tensor peak = "
-                               + ("bf16_tflops_sustained of measured" if peaks else "1.4 PFLOP/s of fallback"),
-                "ms_per_launch": head_ms, "traffic": None,
-                "algorithmic_bytes_per_launch": B * 64 * 750 * 4 + B * n_win * 8 * 32 * 4}
+    alg_bytes = B * 64 * 750 * 4 + B * n_win * 8 * 32 * 4
+    traffic = None
+    tr_path = os.path.join(ROOT, "profiles", "head_fwd_traffic.json")           # dram bytes per launch from ncu --set full
+    if os.path.exists(tr_path):
+        t = json.load(open(tr_path)).get(f"{args.head_precision}@{B}")
+        traffic = t["dram_bytes"] if t else None
+    if n_terms:
+        tensor_peak = peaks.get("bf16_tflops_sustained", 1400.0)                # timed inside a long step -> sustained figure
+        mma = tc_mma_flop_per_window(n_terms) * n_win * B / (head_ms * 1e-3) / 1e12
+        roofline = {"kernel": f"head_fwd_tc_kernel<{n_terms}>", "bound": "tensor", "achieved": ach, "peak": tensor_peak,
+                    "unit": "TFLOP/s", "frac": ach / tensor_peak, "fp32_equivalent_executed": exe,
+                    "bf16_mma_issued": mma, "frac_mma_issued": mma / tensor_peak,
+                    "peak_source": ("bf16_tflops_sustained of measured (MEASURED_PEAKS.json)" if peaks else "1.4 PFLOP/s sustained of fallback"),
+                    "note": "achieved = direct-form (reference) head flops / CUDA-event time of the kernel; each fp32 operand is "
+                            f"{n_terms} bf16 terms, so the tensor pipe issues bf16_mma_issued; the SS-mode N<=96 MMA shape is "
+                            "shared-memory-operand bound at 47-57 cycles per M128 K16 MMA (tools/umma_probe.cu), see DESIGN.md",
+                    "ms_per_launch": head_ms, "traffic": traffic, "algorithmic_bytes_per_launch": alg_bytes}
+    else:
+        fp32_peak = 148 * 128 * 2 * (peaks.get("sm_max_mhz", 1965.0) * 1e6) / 1e12  # FFMA lanes x 2 flop x clock
+        roofline = {"kernel": "head_fwd_kernel<32>", "bound": "fp32-fma (CUDA-core kernel)", "achieved": ach, "peak": fp32_peak,
+                    "unit": "TFLOP/s", "frac": ach / fp32_peak, "fp32_equivalent_executed": exe, "frac_executed": exe / fp32_peak,
+                    "peak_source": "FP32 FMA pipe = 148 SM x 128 lanes x 2 x sm_max_mhz (MEASURED_PEAKS.json clock)",
+                    "ms_per_launch": head_ms, "traffic": traffic, "algorithmic_bytes_per_launch": alg_bytes}
 
     extra = {}
     if not args.no_extras:
         extra = extras(model, cfg, dev, x)
 
     threads = os.cpu_count() or 1
-    n_cpu = 192
-    cpu_v, cpu_s = cpu_forward_trials_per_s(n_cpu, 64, 2, threads)
+    n_cpu = args.cpu_trials
+    cpu_v, cpu_s = cpu_forward_trials_per_s(n_cpu, 256, 1, threads)
     line = {"metric": "FAST inference trials/s", "value": value, "unit": "trials/s", "n_gpus": world, "steps": K, "warmup": W,
-            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": (f"bf16x{n_terms} split operands on tcgen05, f32 accumulate (f32 in / f32 out)" if n_terms else "f32"),
             "data": "synthetic", "config": workload_config(args), "clocks": clocks.summary(),
             "e2e": {"value": e2e_value, "unit": "trials/s", "h2d_bytes_per_step": B * BYTES_PER_TRIAL, "d2h_bytes_per_step": B * 8,
                     "steps": Ke, "ms_per_step": e2e_ms / Ke},
             "gpu_launches": 3 * K, "roofline": roofline,
             "cpu_baseline": {"value": cpu_v, "unit": "trials/s", "cores": threads, "kind": "port",
-                             "sample": f"{n_cpu} trials in chunks of 64, best of 2 ({cpu_s:.1f} s), oracle port of the reference forward"},
+                             "sample": f"{n_cpu} of the {B} trials of one batch, in chunks of 256 ({cpu_s:.1f} s), oracle port of the reference forward"},
             "extra": extra}
     print(json.dumps(line), flush=True)
     if dist is not None:
@@ -308,6 +336,21 @@ def extras(model, cfg, dev, x):
             e1.record()
             torch.cuda.synchronize(dev)
             out["infer_sweep_trials_per_s"][str(b)] = b * n / (e0.elapsed_time(e1) * 1e-3)
+        from fast.models import fast as FM
+        cur = FM.get_head_precision()
+        out["infer_full_batch_by_head_precision"] = {}
+        for mode in ("bf16x3", "bf16x2", "fp32"):                      # same batch, the three head arithmetics
+            FM.set_head_precision(mode)
+            for _ in range(3):
+                model(x)
+            n = 5
+            e0.record()
+            for _ in range(n):
+                model(x).argmax(1)
+            e1.record()
+            torch.cuda.synchronize(dev)
+            out["infer_full_batch_by_head_precision"][mode] = x.shape[0] * n / (e0.elapsed_time(e1) * 1e-3)
+        FM.set_head_precision(cur)
     torch.manual_seed(42)
     tm = FAST(cfg).to(dev).train()
     ft = FusedTrainer(tm, lr=5e-4, use_graph=True)
@@ -337,6 +380,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=8192)
     ap.add_argument("--no-extras", action="store_true")
+    ap.add_argument("--head-precision", default=os.environ.get("FASTB200_HEAD_PRECISION", "bf16x3"), choices=["bf16x3", "bf16x2", "fp32"])
+    ap.add_argument("--e2e-chunk", type=int, default=1024, help="trials per H2D piece of the end-to-end run")
+    ap.add_argument("--cpu-trials", type=int, default=4096, help="trials of the bounded CPU-baseline sample (~10 s)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

@@ -239,6 +239,7 @@ struct Smem {                                  // fixed part at the start of dyn
     uint64_t w_full;
     uint64_t x_full[2], x_empty[2], de_full[2], dm_full[2], ye_ready[2], yc_ready[2], d_free[2];
     uint64_t stg_full[2][2], stg_empty[2][2];
+    uint64_t red_free[2];                      // partial-sum slot of item parity p may be reused (its feature was written)
     uint32_t tmem_base;
     int counter[2];
     float red[2][EPI_WARPS][CW];
@@ -283,6 +284,8 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
             mbar_init(&sm.yc_ready[s], EPI_WARPS * 16);
             mbar_init(&sm.d_free[s], EPI_WARPS * 16);
         }
+        mbar_init(&sm.red_free[0], 1);
+        mbar_init(&sm.red_free[1], 1);
         sm.counter[0] = sm.counter[1] = 0;
         fence_mbar_init();
     }
@@ -565,6 +568,9 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
             }
             v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
             const int par = it & 1;
+            // the two streams have independent issuers and may drift apart: do not touch the slot of item `it` before the
+            // feature of item it - 2 (same slot) has been written
+            if (it >= 2) mbar_wait(&sm.red_free[par], ((it >> 1) - 1) & 1);
             if ((lane & 1) == 0) sm.red[par][warp][lane >> 1] = v[0];
             __syncwarp();
             int old = 0;
@@ -583,7 +589,10 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
                 const int item = rank + it * nz;
                 a.feat[((size_t)item * a.Z + z) * F + lane] = tot / (float)a.T_out;
                 __syncwarp();
-                if (lane == 0) sm.counter[par] = 0;
+                if (lane == 0) {
+                    sm.counter[par] = 0;
+                    mbar_arrive(&sm.red_free[par]);
+                }
             }
             if (PROF) ep[2] += clock64() - c1;
         };

@@ -89,7 +89,8 @@ class FusedTrainer:
 
     # ------------------------------------------------------------------------------------------ workspaces
     def _workspace(self, B, T, label_dtype, train):
-        key = (B, T, label_dtype, train)
+        from ..models import fast as FM
+        key = (B, T, label_dtype, train, None if train else FM.get_head_precision())   # a captured graph bakes the kernel choice in
         ws = self._ws.get(key)
         if ws is not None:
             return ws
@@ -141,9 +142,20 @@ class FusedTrainer:
         lib, d, p = self.lib, self.desc, N.ptr
         st = N.stream_ptr(self.device)
         B, T, n_win = ws["B"], ws["T"], ws["n_win"]
-        N.check(lib.fastb200_head_pack(d, p(self.flat), p(self.packed), st), "head_pack")
-        N.check(lib.fastb200_head_fwd(d, p(self.packed), p(ws["x"]), B, T, n_win, d.slide_step, p(ws["feat"]), None, st),
-                "head_fwd")
+        from ..models import fast as FM
+        n_terms = FM._TERMS[FM.get_head_precision()]
+        if n_terms and lib.fastb200_head_tc_supported(d):
+            # evaluation needs no saved activations: tensor-core head (same dispatch as FAST.forward_head under no_grad)
+            key = ("packed_tc", n_terms)
+            if key not in self._ws:
+                self._ws[key] = torch.empty(lib.fastb200_head_packed_tc_bytes(d, n_terms), device=self.device, dtype=torch.uint8)
+            N.check(lib.fastb200_head_pack_tc(d, p(self.flat), p(self._ws[key]), n_terms, st), "head_pack_tc")
+            N.check(lib.fastb200_head_fwd_tc(d, p(self._ws[key]), p(ws["x"]), B, T, n_win, d.slide_step, p(ws["feat"]),
+                                             n_terms, st), "head_fwd_tc")
+        else:
+            N.check(lib.fastb200_head_pack(d, p(self.flat), p(self.packed), st), "head_pack")
+            N.check(lib.fastb200_head_fwd(d, p(self.packed), p(ws["x"]), B, T, n_win, d.slide_step, p(ws["feat"]), None, st),
+                    "head_fwd")
         N.check(lib.fastb200_transformer_fwd(d, p(self.flat), p(ws["feat"]), B, n_win, self.mode, 0.0, 0, 0, None,
                                              p(ws["logits"]), None, st), "transformer_fwd")
         N.check(lib.fastb200_ce_fwd_bwd(p(ws["logits"]), p(ws["y"]), ws["y"].element_size(), B, d.n_classes, 1.0,

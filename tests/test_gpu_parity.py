@@ -214,6 +214,19 @@ def test_batch_invariance_large(golden):
         parts = torch.cat([m(c) for c in x.split(300)])
     assert torch.equal(full, parts)
     assert torch.isfinite(full).all()
+    # hundreds of items per persistent CTA: the tensor-core head (default) against the exact FFMA head on every trial
+    from fast.models import fast as FM
+    old = FM.get_head_precision()
+    try:
+        feats = {}
+        for mode in ("fp32", "bf16x3", "bf16x2"):
+            FM.set_head_precision(mode)
+            with torch.no_grad():
+                feats[mode] = m.forward_head(x)
+        assert rel_err(feats["bf16x3"], feats["fp32"]) < 5e-6
+        assert rel_err(feats["bf16x2"], feats["fp32"]) < 3e-5
+    finally:
+        FM.set_head_precision(old)
 
 
 # ---------------------------------------------------------------------------------------------- loss / optimiser
@@ -410,3 +423,83 @@ def test_dropout_train_mode_is_consistent():
     m.eval()
     with torch.no_grad():
         assert torch.equal(m(x), m(x))
+
+
+# ---------------------------------------------------------------------------------------------- tensor-core head
+# fastb200_head_fwd_tc (split-bf16 tcgen05 MMAs) against the fp64 oracle.  Bounds: 3 terms = 24 mantissa bits (fp32
+# equivalent; the residual is the 1.5e-7 erfc approximation of the fused GELU), 2 terms = 16 bits.  Both far inside TOL.
+TC_TOL = {"fp32": 2e-6, "bf16x3": 5e-6, "bf16x2": 3e-5}
+
+
+@pytest.fixture
+def head_precision():
+    from fast.models import fast as FM
+    old = FM.get_head_precision()
+    yield FM.set_head_precision
+    FM.set_head_precision(old)
+
+
+def _oracle_feat64(model, cfg, x):
+    sd = {k: v.detach().cpu().double() for k, v in model.state_dict().items()}
+    return O.forward_head(sd, cfg, x.double().cpu())
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16x3", "bf16x2"])
+def test_tc_head_features_vs_fp64_oracle(golden, head_precision, mode):
+    head_precision(mode)
+    cfg = make_prod_cfg(dropout=0.0)
+    m = _prod_model(dropout=0.0).eval()
+    x = _prod_x()
+    with torch.no_grad():
+        feat = m.forward_head(x.cuda())
+        assert rel_err(feat, golden["prod/feat"]) < TOL                      # the real reference's output
+        assert rel_err(feat, _oracle_feat64(m, cfg, x)) < TC_TOL[mode]
+        # large, offset inputs (uV-scale EEG with a DC offset): operand splitting has to hold its relative accuracy
+        xb = x * 40.0 + 25.0
+        assert rel_err(m.forward_head(xb.cuda()), _oracle_feat64(m, cfg, xb)) < TC_TOL[mode]
+        assert rel_err(m(x.cuda() * 30.0), golden["prod/logits_x30"]) < TOL
+
+
+@pytest.mark.parametrize("mode", ["bf16x3", "bf16x2"])
+def test_tc_head_batches_windows_and_determinism(head_precision, mode):
+    head_precision(mode)
+    cfg = make_prod_cfg(dropout=0.0)
+    m = _prod_model(dropout=0.0).eval()
+    g = torch.Generator().manual_seed(7)
+    with torch.no_grad():
+        for B, T in ((1, 795), (3, 800), (37, 795), (300, 1050)):           # 1050 samples: 7 windows (forward_head only)
+            x = torch.randn(B, 64, T, generator=g) * 3.0
+            f = m.forward_head(x.cuda())
+            assert f.shape == (B, (T - 250) // 125 + 1, 8, 32)
+            assert rel_err(f, _oracle_feat64(m, cfg, x)) < TC_TOL[mode]
+            assert torch.equal(f, m.forward_head(x.cuda()))                 # fixed-order reductions: bit reproducible
+            assert torch.equal(m.batched_forward_head(x.cuda(), 125, 16), f)  # per-item result independent of the batch
+        x = torch.randn(5, 64, 800, generator=g)
+        f50 = m.forward_head(x.cuda(), 50)                                   # step_override (reference fast.py:243-246)
+        assert f50.shape == (5, 12, 8, 32)
+        assert rel_err(f50, O.forward_head({k: v.detach().cpu().double() for k, v in m.state_dict().items()}, cfg,
+                                           x.double(), 50)) < TC_TOL[mode]
+        assert m.forward_head(x[:0].cuda()).shape == (0, 5, 8, 32)
+
+
+def test_tc_head_zone_sizes_and_fallback(head_precision):
+    """Zones of 1, 8, 9 and 16 electrodes (both electrode-tile layouts of the kernel); shapes the tensor-core kernel does not
+    cover (window_len 120, dim_cnn 16, a 20-electrode zone) silently take the FFMA kernel -- still a CUDA kernel."""
+    from fast.models import FAST
+    from fast import _native as N
+    head_precision("bf16x3")
+    names = [f"E{i}" for i in range(40)]
+    zones = {"one": names[:1], "eight": names[1:9], "nine": names[9:18], "sixteen": names[18:34], "rest": names[34:40]}
+    base = dict(electrodes=names, zone_dict=zones, dim_cnn=32, dim_token=32, seq_len=500, window_len=250, slide_step=125,
+                head="Conv4Layers", n_classes=4, num_layers=1, num_heads=4, dropout=0.0)
+    x = torch.randn(6, 40, 500, generator=torch.Generator().manual_seed(3)) * 2.0
+    for over, tc in ((dict(), True), (dict(window_len=120, slide_step=60), False), (dict(dim_cnn=16), False),
+                     (dict(zone_dict={"big": names[:20], "rest": names[20:]}), False)):
+        cfg = make_small_cfg(**{**base, **over})
+        torch.manual_seed(11)
+        m = FAST(cfg).cuda().eval()
+        _, desc = m._runtime()
+        assert bool(N.lib().fastb200_head_tc_supported(desc)) == tc
+        with torch.no_grad():
+            f = m.forward_head(x.cuda())
+        assert rel_err(f, _oracle_feat64(m, cfg, x)) < TC_TOL["bf16x3"]
