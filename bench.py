@@ -372,6 +372,339 @@ def extras(model, cfg, dev, x):
     return out
 
 
+# ------------------------------------------------------------------------------------------------ other workloads
+def _dist_setup(world, local_rank):
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    return dev, dist
+
+
+def _max_over_ranks(ms, dist, dev):
+    if dist is None:
+        return ms
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t)
+
+
+def _emit(line, dist, rank):
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def run_train(args, rank, world, local_rank):
+    """FAST training step (fwd + CE + bwd + AdamW) -- BASELINE metric 'train fwd+bwd' and configs[0]'s batch 64.
+    Weak scaling: every rank trains its own replica on its own batch (the CV regime: independent jobs)."""
+    dev, dist = _dist_setup(world, local_rank)
+    from fast.models import FAST
+    from fast.train import FusedTrainer
+    from fast.models import fast as FM
+    FM.set_head_precision(args.head_precision)
+    cfg = prod_cfg()
+    B, K, W = args.batch, args.steps, args.warmup
+    torch.manual_seed(42 + rank)
+    model = FAST(cfg).to(dev).train()
+    ft = FusedTrainer(model, lr=5e-4, use_graph=True)
+    nb = max(2, -(-200_000_000 // (B * BYTES_PER_TRIAL)))          # rotate over > L2 worth of distinct batches
+    xs = torch.randn(nb, B, 64, 795, device=dev)
+    ys = torch.randint(0, 5, (nb, B), device=dev).to(torch.uint8)
+    for i in range(W):
+        ft.train_step(xs[i % nb], ys[i % nb])
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clocks:
+        e0.record()
+        for i in range(K):
+            ft.train_step(xs[i % nb], ys[i % nb])
+        e1.record()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+    ms = _max_over_ranks(e0.elapsed_time(e1), dist, dev)
+    value = world * B * K / (ms * 1e-3)
+    # end to end: batch in pinned host memory, loss read back
+    xh = torch.empty(B, 64, 795).pin_memory(); xh.copy_(xs[0])
+    yh = ys[0].cpu().pin_memory()
+    lh = torch.empty(1).pin_memory()
+    for _ in range(3):
+        ft.train_step(xh.to(dev, non_blocking=True), yh.to(dev, non_blocking=True))
+    torch.cuda.synchronize(dev)
+    Ke = max(3, K // 2)
+    e0.record()
+    for _ in range(Ke):
+        loss, _ = ft.train_step(xh.to(dev, non_blocking=True), yh.to(dev, non_blocking=True))
+        lh.copy_(loss, non_blocking=True)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    e2e_ms = _max_over_ranks(e0.elapsed_time(e1), dist, dev)
+    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+    fp32_peak = 148 * 128 * 2 * (peaks.get("sm_max_mhz", 1965.0) * 1e6) / 1e12
+    ach = FLOP_TRAIN_DIRECT * B * K / (ms * 1e-3) / 1e12 / 1.0
+    cpu = None
+    if rank == 0 and not args.no_extras:
+        cpu = cpu_train_trials_per_s(64, os.cpu_count() or 1)
+    line = {"metric": "FAST training trials/s (fwd+bwd+AdamW)", "value": value, "unit": "trials/s", "n_gpus": world, "steps": K,
+            "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "clocks": clocks.summary(),
+            "config": {"workload": "FAST training step, production config, dropout 0.1 (BASELINE metric 'train fwd+bwd'; configs[0] batch = 64)",
+                       "batch_per_gpu": B, "channels": 64, "samples": 795, "l2_policy": f"{nb} distinct resident batches rotated (> 126 MB)",
+                       "parallelism": f"independent replicas x{world} (CV regime), no collective"},
+            "e2e": {"value": world * B * Ke / (e2e_ms * 1e-3), "unit": "trials/s", "h2d_bytes_per_step": B * BYTES_PER_TRIAL + B,
+                    "d2h_bytes_per_step": 4, "steps": Ke},
+            "gpu_launches": ft.LAUNCHES_TRAIN * K,
+            "roofline": {"kernel": "whole step (head_fwd + head_bwd dominate)", "bound": "fp32-fma (CUDA-core kernels)",
+                         "achieved": ach / world, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / world / fp32_peak, "traffic": None,
+                         "note": "direct-form training flops (SURVEY 8d: 1,140,087,744 per trial) / step time, per GPU"},
+            "cpu_baseline": cpu}
+    _emit(line, dist, rank)
+
+
+def cpu_train_trials_per_s(batch, threads):
+    """Oracle port of the reference's training step (CE + autograd + AdamW, trainer.py:48-67) on the host cores."""
+    from fast.models import FAST
+    from oracle import fast_oracle as O
+    torch.set_num_threads(threads)
+    cfg = prod_cfg(dropout=0.0)
+    torch.manual_seed(42)
+    sd = {k: v.detach().clone() for k, v in FAST(cfg).state_dict().items()}
+    m = {k: torch.zeros_like(v) for k, v in sd.items()}
+    v = {k: torch.zeros_like(t) for k, t in sd.items()}
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(batch, 64, 795, generator=g)
+    y = torch.randint(0, 5, (batch,), generator=g)
+    ts = []
+    for step in range(1, 4):
+        t0 = time.perf_counter()
+        _, _, grads, _ = O.loss_and_grads(sd, cfg, x, y)
+        for k in sd:
+            O.adamw_step(sd[k], grads[k], m[k], v[k], step, 5e-4)
+        ts.append(time.perf_counter() - t0)
+    best = min(ts[1:])
+    return {"value": batch / best, "unit": "trials/s", "cores": threads, "kind": "port",
+            "sample": f"one batch of {batch} trials per step, best of 2 after 1 warm-up ({best:.1f} s/step), oracle port of the training step"}
+
+
+def run_preprocess(args, rank, world, local_rank):
+    """BASELINE configs[2]: zero-phase Butterworth band-pass + 4/5 polyphase resample of 15 subjects x 400 trials
+    (SURVEY 8d-D3), subjects sharded over ranks (no collective)."""
+    dev, dist = _dist_setup(world, local_rank)
+    from fast.data import filters as F
+    from oracle import filter_oracle as FO
+    subs = list(range(15))[rank::world]
+    n_tr = 400
+    xs = []
+    for s_ in subs:
+        rng = np.random.default_rng(1000 + s_)
+        x = (20 * rng.standard_normal((n_tr, 64, 795)) + rng.uniform(-50, 50, (1, 64, 1))).astype(np.float32)
+        xs.append(torch.from_numpy(x).to(dev))
+    sos = F.bandpass_sos()
+
+    def step():
+        out = None
+        for x in xs:
+            out = F.resample_poly(F.sosfiltfilt(sos, x, out_dtype=torch.float64), 4, 5, out_dtype=torch.float32)
+        return out
+
+    K, W = args.steps, args.warmup
+    for _ in range(W):
+        step()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clocks:
+        e0.record()
+        for _ in range(K):
+            step()
+        e1.record()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+    ms = _max_over_ranks(e0.elapsed_time(e1), dist, dev)
+    # the filter kernel alone (dominant), f32 in -> f64 out as the chain uses it
+    f0.record()
+    for _ in range(K):
+        for x in xs:
+            F.sosfiltfilt(sos, x, out_dtype=torch.float64)
+    f1.record()
+    torch.cuda.synchronize(dev)
+    filt_ms = f0.elapsed_time(f1) / (K * max(1, len(xs)))
+    total_trials = 15 * n_tr
+    value = total_trials * K / (ms * 1e-3)
+    # end to end from pinned host memory
+    xh = [x.cpu().pin_memory() for x in xs]
+    outh = [torch.empty(n_tr, 64, 636).pin_memory() for _ in xs]
+    torch.cuda.synchronize(dev)
+    e0.record()
+    for xi, oi in zip(xh, outh):
+        xd = xi.to(dev, non_blocking=True)
+        oi.copy_(F.resample_poly(F.sosfiltfilt(sos, xd, out_dtype=torch.float64), 4, 5, out_dtype=torch.float32), non_blocking=True)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    e2e_ms = _max_over_ranks(e0.elapsed_time(e1), dist, dev)
+    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+    hbm = peaks.get("hbm_gbs", 6500.0)
+    alg = n_tr * 64 * 795 * (4 + 8)                                     # f32 read + f64 write per launch
+    cpu = None
+    if rank == 0:
+        nc = 2
+        xc = xs[0][:nc].cpu().numpy().reshape(-1, 795)
+        t0 = time.perf_counter()
+        yc = FO.sosfiltfilt(sos, xc)
+        FO.resample_poly(yc, 4, 5)
+        dt = time.perf_counter() - t0
+        cpu = {"value": nc / dt, "unit": "trials/s", "cores": 1, "kind": "port",
+               "sample": f"{nc} trials x 64 channels ({dt:.1f} s), NumPy float64 oracle port of scipy sosfiltfilt + resample_poly"}
+    line = {"metric": "preprocessing trials/s (sosfiltfilt 4-40 Hz order 4 + resample_poly 4/5)", "value": value, "unit": "trials/s",
+            "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64 (f32 in, f32 out)", "data": "synthetic", "clocks": clocks.summary(),
+            "config": {"workload": "BASELINE configs[2]: 15 subjects x 400 trials x 64 ch x 795 samples", "subjects_this_rank": len(subs),
+                       "l2_policy": "every subject's block is 81 MB in / 163 MB intermediate; 15 blocks per step (> 126 MB L2)",
+                       "parallelism": f"subjects sharded x{world}, no collective"},
+            "e2e": {"value": total_trials / (e2e_ms * 1e-3),
+                    "unit": "trials/s", "h2d_bytes_per_step": len(subs) * n_tr * 64 * 795 * 4, "d2h_bytes_per_step": len(subs) * n_tr * 64 * 636 * 4},
+            "gpu_launches": 2 * len(xs) * K,
+            "roofline": {"kernel": "sosfiltfilt_kernel", "bound": "hbm", "achieved": alg / (filt_ms * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
+                         "frac": alg / (filt_ms * 1e-3) / 1e9 / hbm, "traffic": None, "ms_per_launch": filt_ms,
+                         "algorithmic_bytes_per_launch": alg},
+            "cpu_baseline": cpu}
+    _emit(line, dist, rank)
+
+
+def run_cv(args, rank, world, local_rank):
+    """BASELINE configs[3]: 15 subjects x 5 folds of FAST training, jobs sharded over ranks (strong scaling, no data-path
+    collective), synthetic subjects.  value = wall-clock seconds from first dispatch to the last result."""
+    import shutil
+    import tempfile
+    dev, dist = _dist_setup(world, local_rank)
+    from fast.data import SUBJECTS
+    from fast.train import cv as CV
+    cfg = prod_cfg()
+    subjects = SUBJECTS[:args.subjects]
+    jobs = CV.cv_jobs(subjects, 5)
+    mine = CV.shard_jobs(jobs, rank, world)
+    save = args.cv_dir or os.path.join(tempfile.gettempdir(), "fastb200_cv")
+    if rank == 0:
+        shutil.rmtree(save, ignore_errors=True)
+        os.makedirs(save, exist_ok=True)
+    data = {}
+
+    def load(sid):
+        if sid not in data:
+            data.clear()
+            data[sid] = CV.synthetic_subject(int(sid) - 1)
+        return data[sid][0]
+
+    # warm-up: one short job compiles nothing but builds graphs / primes allocators (not part of the 75 jobs)
+    CV.run_cv_jobs(cfg, [(0, "warm", 0)], lambda s: CV.synthetic_subject(99)[0], os.path.join(save, f"_warm{rank}"), max_epochs=2,
+                   batch_size=args.cv_batch, seed=1)
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    with ClockSampler(local_rank) as clocks:
+        t0 = time.perf_counter()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        done = CV.run_cv_jobs(cfg, mine, load, save, max_epochs=args.epochs, batch_size=args.cv_batch, seed=42, resume=False)
+        e1.record()
+        torch.cuda.synchronize(dev)
+        dev_s = e0.elapsed_time(e1) * 1e-3
+        if dist is not None:
+            dist.barrier()
+        wall = time.perf_counter() - t0
+    dev_s = _max_over_ranks(dev_s, dist, dev)
+    wall = _max_over_ranks(wall, dist, dev)
+    rows = []
+    if rank == 0:
+        tests = {sid: CV.synthetic_subject(int(sid) - 1)[1] for sid in subjects}
+        rows = CV.finalize_cv(cfg, subjects, save, n_folds=5, test_per_subject=tests)
+    n_train_trials = len(jobs) * args.epochs * 280
+    steps = len(jobs) * args.epochs * 5
+    line = {"metric": "15-subject x 5-fold CV wall-clock", "value": dev_s, "unit": "s", "n_gpus": world, "steps": steps, "warmup": 1,
+            "ms_per_step": 1e3 * dev_s / max(1, len(mine) * args.epochs * 5), "higher_is_better": False, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32 train / bf16x3 eval", "data": "synthetic", "clocks": clocks.summary(),
+            "config": {"workload": "BASELINE configs[3]: per-subject 5-fold CV of FAST, batch 64", "jobs": len(jobs), "jobs_this_rank": len(mine),
+                       "epochs": args.epochs, "subjects": len(subjects), "trials_per_subject": 350, "batch": args.cv_batch,
+                       "parallelism": f"subject x fold jobs sharded x{world}, no collective", "host_wall_s": wall,
+                       "ideal_rounds": -(-len(jobs) // world)},
+            "train_trials_per_s": n_train_trials / dev_s, "subjects_done": len(rows),
+            "mean_test_acc": (float(np.mean([r[2] for r in rows])) if rows else None),
+            "e2e": {"value": wall, "unit": "s", "h2d_bytes_per_step": 350 * 64 * 800 * 4 // (5 * args.epochs * 5), "d2h_bytes_per_step": 0},
+            "gpu_launches": len(mine) * args.epochs * (5 * 9 + 4)}
+    _emit(line, dist, rank)
+
+
+def run_stress(args, rank, world, local_rank):
+    """BASELINE configs[4]: 64 ch x 4000-sample trials (31 windows, 32 tokens), data-parallel training with the flat
+    gradient exchanged every step.  Weak scaling: args.batch trials per GPU (512 x 8 = 4096 at 8 GPUs)."""
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(local_rank)
+    import torch.distributed as dist
+    if world == 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1"); os.environ.setdefault("MASTER_PORT", "29533")
+        dist.init_process_group("nccl", rank=0, world_size=1, device_id=dev)
+    else:
+        dist.init_process_group("nccl", device_id=dev)
+    from fast.models import FAST
+    from fast.train import DataParallelTrainer
+    cfg = prod_cfg()
+    cfg.seq_len = 4000
+    B, K, W = args.batch, args.steps, args.warmup
+    torch.manual_seed(42)
+    model = FAST(cfg).to(dev).train()
+    ft = DataParallelTrainer(model, reduce=args.reduce, lr=5e-4, use_graph=True)
+    gen = torch.Generator(device=dev).manual_seed(rank)
+    x = torch.randn(B, 64, 4000, device=dev, generator=gen)
+    y = torch.randint(0, 5, (B,), device=dev, generator=gen).to(torch.uint8)
+    for _ in range(W):
+        ft.train_step(x, y)
+    dist.barrier(); torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clocks:
+        e0.record()
+        for _ in range(K):
+            ft.train_step(x, y)
+        e1.record()
+        dist.barrier(); torch.cuda.synchronize(dev)
+    ms = _max_over_ranks(e0.elapsed_time(e1), dist, dev)
+    # exposed exchange time: the same K steps of the update phase alone (barrier + fused reduce/AdamW or NCCL + AdamW)
+    ws = next(w for k, w in ft._ws.items() if isinstance(w, dict) and w.get("graph"))
+    upd = [fn for fn in ws["graph"][1:]] if world > 1 else []
+    e0.record()
+    for _ in range(K):
+        for fn in upd:
+            fn()
+    e1.record()
+    torch.cuda.synchronize(dev)
+    upd_ms = e0.elapsed_time(e1) / K if upd else 0.0
+    loss, _ = ft.global_loss_and_correct()
+    flop = 2.0 * (31 * (38_793_216 + 75_067_392) + 3 * 1_564_832) * 1.0
+    line = {"metric": "FAST stress training trials/s (64 ch x 4000 samples, data-parallel)", "value": world * B * K / (ms * 1e-3),
+            "unit": "trials/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "clocks": clocks.summary(),
+            "config": {"workload": "BASELINE configs[4]: seq_len 4000 (31 windows, 32 tokens), DP", "batch_per_gpu": B,
+                       "global_batch": B * world, "reduce": args.reduce if world > 1 else "none",
+                       "l2_policy": f"input {B * 64 * 4000 * 4 / 1e9:.2f} GB per step > 126 MB L2",
+                       "parallelism": f"dp{world}: one flat 767 KB gradient exchange per step"},
+            "exchange_plus_update_ms": upd_ms, "loss": loss,
+            "e2e": None, "gpu_launches": 9 * K,
+            "roofline": {"kernel": "whole step", "bound": "fp32-fma", "achieved": flop * B * K / (ms * 1e-3) / 1e12,
+                         "peak": 148 * 128 * 2 * 1.965e9 / 1e12, "unit": "TFLOP/s",
+                         "frac": flop * B * K / (ms * 1e-3) / 1e12 / (148 * 128 * 2 * 1.965e9 / 1e12), "traffic": None}}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -383,6 +716,13 @@ def main():
     ap.add_argument("--head-precision", default=os.environ.get("FASTB200_HEAD_PRECISION", "bf16x3"), choices=["bf16x3", "bf16x2", "fp32"])
     ap.add_argument("--e2e-chunk", type=int, default=1024, help="trials per H2D piece of the end-to-end run")
     ap.add_argument("--cpu-trials", type=int, default=4096, help="trials of the bounded CPU-baseline sample (~10 s)")
+    ap.add_argument("--workload", default="infer", choices=["infer", "train", "preprocess", "cv", "stress"],
+                    help="infer = the headline (BASELINE configs[1]); the others measure configs[0]/[2]/[3]/[4]")
+    ap.add_argument("--epochs", type=int, default=200, help="cv: epochs per fold (reference: 200)")
+    ap.add_argument("--subjects", type=int, default=15, help="cv: number of synthetic subjects")
+    ap.add_argument("--cv-batch", type=int, default=64)
+    ap.add_argument("--cv-dir", default=None)
+    ap.add_argument("--reduce", default="p2p", choices=["p2p", "nccl"], help="stress: gradient exchange")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -390,6 +730,10 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         run_reference(args, rank)
+    elif args.workload != "infer":
+        if "--batch" not in sys.argv:
+            args.batch = {"train": 1024, "stress": 512}.get(args.workload, args.batch)
+        {"train": run_train, "preprocess": run_preprocess, "cv": run_cv, "stress": run_stress}[args.workload](args, rank, world, local_rank)
     else:
         run_b200(args, rank, world, local_rank)
 

@@ -57,7 +57,12 @@ __global__ void ce_kernel(const float* __restrict__ logits, const LabelT* __rest
 
 // Scalars follow torch's single-tensor AdamW: Python-double hyper-parameter arithmetic, rounded to fp32 once
 // where torch hands them to an fp32 tensor op.
-__global__ void adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+// PEERS > 0: `g` is ignored and the gradient of element i is the sum over `peers.ptr[r][i]`, r = 0 .. n_peers-1 in rank
+// order (so every rank forms bit-identical sums) -- a one-shot all-reduce over NVLink peer memory fused into the update.
+struct PeerGrads { const float* ptr[FASTB200_MAX_PEERS]; int n; };
+
+template <bool PEERS>
+__global__ void adamw_kernel(float* __restrict__ p, const float* __restrict__ g, PeerGrads peers, float* __restrict__ m,
                              float* __restrict__ v, int64_t n, const float* __restrict__ lr_dev, int lr_by_step,
                              double beta1, double beta2, double eps_d, double wd,
                              const int32_t* __restrict__ step_dev) {
@@ -76,7 +81,13 @@ __global__ void adamw_kernel(float* __restrict__ p, const float* __restrict__ g,
     const float step_size = s_c[0], bc2_sqrt = s_c[1], decay = s_c[2];
     const float w1 = (float)(1.0 - beta1), b2 = (float)beta2, w2 = (float)(1.0 - beta2), eps = (float)eps_d;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        const float gi = g[i];
+        float gi;
+        if constexpr (PEERS) {
+            gi = __ldcv(peers.ptr[0] + i);                    // peer memory: never serve from a stale L1 line
+            for (int r = 1; r < peers.n; ++r) gi += __ldcv(peers.ptr[r] + i);
+        } else {
+            gi = g[i];
+        }
         float pi = p[i] * decay;
         float mi = m[i];
         mi = mi + (gi - mi) * w1;                             // exp_avg.lerp_(grad, 1 - beta1)
@@ -134,8 +145,33 @@ extern "C" int fastb200_adamw_flat(float* p, const float* g, float* m, float* v,
     if (n == 0) return 0;
     int64_t blocks = (n + 255) / 256;
     if (blocks > NUM_SMS * 8) blocks = NUM_SMS * 8;
-    adamw_kernel<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(p, g, m, v, n, lr_dev, lr_by_step, beta1, beta2, eps, weight_decay, step_dev);
+    adamw_kernel<false><<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(p, g, PeerGrads{}, m, v, n, lr_dev, lr_by_step, beta1, beta2, eps, weight_decay, step_dev);
     if (int r = check_launch("adamw_flat")) return r;
+    if (bump_step) {
+        bump_step_kernel<<<1, 1, 0, as_stream(stream)>>>(step_dev);
+        return check_launch("adamw_bump_step");
+    }
+    return 0;
+}
+
+extern "C" int fastb200_adamw_flat_peers(float* p, const float* const* peer_grads_host, int n_peers, float* m, float* v,
+                                         int64_t n, const float* lr_dev, int lr_by_step, double beta1, double beta2,
+                                         double eps, double weight_decay, int32_t* step_dev, int bump_step,
+                                         void* stream) {
+    FB_REQUIRE(n >= 0, "bad n");
+    FB_REQUIRE(n_peers >= 1 && n_peers <= FASTB200_MAX_PEERS, "n_peers must be 1..FASTB200_MAX_PEERS");
+    FB_REQUIRE(peer_grads_host != nullptr, "peer_grads is NULL");
+    PeerGrads pg{};
+    pg.n = n_peers;
+    for (int r = 0; r < n_peers; ++r) {
+        FB_REQUIRE(peer_grads_host[r] != nullptr, "a peer gradient pointer is NULL");
+        pg.ptr[r] = peer_grads_host[r];
+    }
+    if (n == 0) return 0;
+    int64_t blocks = (n + 255) / 256;
+    if (blocks > NUM_SMS * 8) blocks = NUM_SMS * 8;
+    adamw_kernel<true><<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(p, nullptr, pg, m, v, n, lr_dev, lr_by_step, beta1, beta2, eps, weight_decay, step_dev);
+    if (int r = check_launch("adamw_flat_peers")) return r;
     if (bump_step) {
         bump_step_kernel<<<1, 1, 0, as_stream(stream)>>>(step_dev);
         return check_launch("adamw_bump_step");

@@ -66,6 +66,8 @@ SIGNATURES = {
     "fastb200_ce_fwd_bwd": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_float, _P, _P, _P, _P, _P]),
     "fastb200_adamw_flat": (C.c_int, [_P, _P, _P, _P, C.c_int64, _P, C.c_int, C.c_double, C.c_double, C.c_double,
                                       C.c_double, _P, C.c_int, _P]),
+    "fastb200_adamw_flat_peers": (C.c_int, [_P, C.POINTER(C.c_void_p), C.c_int, _P, _P, C.c_int64, _P, C.c_int, C.c_double,
+                                            C.c_double, C.c_double, C.c_double, _P, C.c_int, _P]),
     "fastb200_trials_from_mat": (C.c_int, [_P, C.c_int, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
     "fastb200_sosfiltfilt": (C.c_int, [_P, C.c_int, _P, C.c_int, C.c_int64, C.c_int, C.POINTER(C.c_double), C.c_int,
                                        C.c_int, _P]),

@@ -1,0 +1,277 @@
+"""Per-subject k-fold cross-validation of FAST, sharded over GPUs as independent jobs
+(the throughput path behind ``finetune_per_subject_cv``, reference scripts/train_fast.py:68-262).
+
+The 15 subjects x 5 folds are 75 jobs that share nothing (each builds a fresh model, train_fast.py:113), so ranks take
+jobs and there is NO data-path collective; the only join is on the host: per subject "best of the folds -> that
+subject's test set" (train_fast.py:182-212) and the summary CSVs (:226-240).
+
+One job = the reference's ``trainer.fit`` for one fold, with the Lightning loop replaced by a device-resident loop:
+the subject's trials stay in HBM (72 MB), batches are index gathers on the device, every step is the CUDA-graphed
+``FusedTrainer`` step, metrics accumulate on the device and the best-``val_acc`` weights are kept by a predicated
+device copy -- the host never synchronises inside a job.  Artefacts keep the reference's names and formats
+(``sub-XX/fold-k_history.csv``, ``fold_metrics.csv``, ``best_subject.pth``, ``test_predictions.csv``,
+``summary_per_subject.csv``, ``global_test_predictions.csv``) so ``scripts/benchmark.py`` reads them unchanged.
+
+Documented deviation: the reference seeds once before all loops, so job k's initial weights and
+shuffles depend on every job before it; sharded jobs cannot reproduce that stream and use per-job seeds
+``seed + n_folds * subject_index + fold`` instead.
+"""
+from __future__ import annotations
+
+import csv
+import json
+import math
+import os
+
+import numpy as np
+import torch
+
+from .fused import FusedTrainer, lightning_lr_factors
+from .trainer import cosine_scheduler
+
+
+# ---------------------------------------------------------------------------------------------------- host logic
+def kfold_indices(n_samples: int, n_splits: int, shuffle: bool = True, random_state=None):
+    """[(train_idx, val_idx)] exactly as ``sklearn.model_selection.KFold(n_splits, shuffle, random_state).split``
+    (used at train_fast.py:94): a ``RandomState(seed).shuffle`` of ``arange(n)``, then contiguous folds whose first
+    ``n % k`` members have one extra sample; the train indices keep ascending order."""
+    if n_splits < 2 or n_splits > n_samples:
+        raise ValueError(f"n_splits={n_splits} must be in [2, n_samples={n_samples}]")
+    idx = np.arange(n_samples)
+    if shuffle:
+        np.random.RandomState(random_state).shuffle(idx)
+    sizes = np.full(n_splits, n_samples // n_splits, dtype=int)
+    sizes[:n_samples % n_splits] += 1
+    out, cur = [], 0
+    for s in sizes:
+        mask = np.zeros(n_samples, dtype=bool)
+        mask[idx[cur:cur + s]] = True
+        out.append((np.flatnonzero(~mask), np.flatnonzero(mask)))
+        cur += s
+    return out
+
+
+def cv_jobs(subjects, n_folds):
+    """All (subject_index, subject_id, fold) jobs in the reference's loop order (train_fast.py:86,100)."""
+    return [(si, sid, k) for si, sid in enumerate(subjects) for k in range(n_folds)]
+
+
+def shard_jobs(jobs, rank: int, world: int):
+    """Static interleaved partition: rank r takes jobs r, r + world, ...  Every job has the same cost (same trial count,
+    epochs and model), so this is balanced to within one job: ceil(75 / g) rounds at g GPUs."""
+    if not 0 <= rank < world:
+        raise ValueError(f"rank {rank} outside world {world}")
+    return list(jobs[rank::world])
+
+
+class JobQueue:
+    """Dynamic alternative to ``shard_jobs``: an atomic counter in the torch.distributed key-value store hands out job
+    indices, so a rank that finishes early takes the next job (no collective, works before/without NCCL)."""
+
+    def __init__(self, jobs, store=None, key="fastb200/cv/next"):
+        self.jobs, self.store, self.key, self._local = list(jobs), store, key, 0
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        i = (self.store.add(self.key, 1) - 1) if self.store is not None else self._local
+        self._local += 1
+        if i >= len(self.jobs):
+            raise StopIteration
+        return self.jobs[i]
+
+
+def job_seed(seed: int, n_folds: int, subject_index: int, fold: int) -> int:
+    return int(seed) + n_folds * int(subject_index) + int(fold)
+
+
+def pick_best_fold(fold_best):
+    """Index of the fold whose checkpoint the reference evaluates: strict ``>`` scan in fold order
+    (train_fast.py:182-185), so ties go to the earliest fold."""
+    best, best_k = -np.inf, None
+    for k, v in fold_best:
+        if v > best:
+            best, best_k = v, k
+    return best_k, best
+
+
+def macro_f1(y_true, y_pred, n_classes=None):
+    """``sklearn.metrics.f1_score(average='macro')`` over the labels present in y_true or y_pred (train_fast.py:214)."""
+    y_true, y_pred = np.asarray(y_true).astype(int), np.asarray(y_pred).astype(int)
+    labels = np.union1d(y_true, y_pred) if n_classes is None else np.arange(n_classes)
+    f = []
+    for c in labels:
+        tp = np.sum((y_true == c) & (y_pred == c))
+        d = np.sum(y_true == c) + np.sum(y_pred == c)
+        f.append(2.0 * tp / d if d else 0.0)
+    return float(np.mean(f)) if f else 0.0
+
+
+# ---------------------------------------------------------------------------------------------------- one fold on the device
+def train_fold(config, x, y, train_idx, val_idx, max_epochs=200, batch_size=64, seed=42, lr=5e-4, warmup_epochs=10,
+               use_graph=True, model=None):
+    """``trainer.fit`` of one fold (train_fast.py:100-140) without Lightning.
+
+    x (n, C, T) float32 and y (n,) uint8/int64 are CUDA tensors holding the subject's train+val trials; train_idx /
+    val_idx index them.  Returns a dict of host values read ONCE at the end of the job:
+    ``history`` {'loss','acc','val_loss','val_acc'} per epoch (the HistoryCallback keys, callbacks.py:12),
+    ``best_val_acc``, ``best_epoch`` and ``state_dict`` of the best epoch (ModelCheckpoint monitor='val_acc' mode='max'
+    top-1: replaced only on a strictly better epoch, train_fast.py:118-125)."""
+    from ..models import FAST
+    dev = x.device
+    if not x.is_cuda:
+        raise RuntimeError("train_fold keeps the subject's trials resident on a CUDA device (there is no CPU fallback)")
+    torch.manual_seed(seed)
+    if model is None:
+        model = FAST(config)
+    model = model.to(dev).train()
+    tr = torch.as_tensor(np.asarray(train_idx), device=dev, dtype=torch.int64)
+    va = torch.as_tensor(np.asarray(val_idx), device=dev, dtype=torch.int64)
+    n_tr, n_va = tr.numel(), va.numel()
+    n_it = math.ceil(n_tr / batch_size)                       # len(train_loader)
+    if warmup_epochs > max_epochs:                            # the stock warmup_epochs=10 asserts for short runs
+        warmup_epochs = 0
+    sched = cosine_scheduler(1, 0.1, max_epochs, n_it, warmup_epochs=warmup_epochs)
+    ft = FusedTrainer(model, lr=lr, lr_factors=lightning_lr_factors(sched), use_graph=use_graph, seed=seed)
+    gen = torch.Generator(device=dev).manual_seed(seed)
+    xv, yv = x[va], y[va]
+    hist = torch.zeros(max_epochs, 4, device=dev, dtype=torch.float64)
+    best_correct = torch.full((1,), -1, device=dev, dtype=torch.int32)
+    best_epoch = torch.zeros(1, device=dev, dtype=torch.int32)
+    best_flat = ft.flat.clone()
+    loss_sum = torch.zeros(1, device=dev, dtype=torch.float64)
+    corr_sum = torch.zeros(1, device=dev, dtype=torch.int64)
+    for ep in range(max_epochs):
+        model.train()
+        perm = tr[torch.randperm(n_tr, device=dev, generator=gen)]
+        loss_sum.zero_(); corr_sum.zero_()
+        for lo in range(0, n_tr, batch_size):
+            idx = perm[lo:lo + batch_size]
+            loss, ncorr = ft.train_step(x[idx], y[idx])
+            loss_sum += loss.double() * idx.numel()          # Lightning's on_epoch mean is batch-size weighted
+            corr_sum += ncorr
+        model.eval()
+        vloss, vcorr, _ = ft.eval_step(xv, yv)
+        hist[ep, 0] = (loss_sum / n_tr)[0]
+        hist[ep, 1] = (corr_sum.double() / n_tr)[0]
+        hist[ep, 2] = vloss[0].double()
+        hist[ep, 3] = vcorr[0].double() / n_va
+        better = vcorr > best_correct                         # (1,) bool, stays on the device
+        best_flat = torch.where(better, ft.flat, best_flat)
+        best_epoch = torch.where(better, torch.full_like(best_epoch, ep), best_epoch)
+        best_correct = torch.maximum(best_correct, vcorr)
+    h = hist.cpu().numpy()                                    # the job's single host synchronisation
+    with torch.no_grad():
+        final = ft.flat.clone()
+        ft.flat.copy_(best_flat)
+        best_sd = {k: v.detach().cpu().clone() for k, v in model.state_dict().items()}
+        ft.flat.copy_(final)
+    return {"history": {"loss": h[:, 0].tolist(), "acc": h[:, 1].tolist(), "val_loss": h[:, 2].tolist(),
+                        "val_acc": h[:, 3].tolist()},
+            "best_val_acc": float(best_correct.item()) / n_va, "best_epoch": int(best_epoch.item()),
+            "train_len": n_it, "steps": ft.steps_done, "state_dict": best_sd}
+
+
+# ---------------------------------------------------------------------------------------------------- the sharded run
+def _write_history(path, history):
+    keys = list(history.keys())
+    with open(path, "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow(["Epoch"] + keys)                          # pandas to_csv(index_label='Epoch'), train_fast.py:150
+        for i in range(min(len(v) for v in history.values())):
+            w.writerow([i] + [history[k][i] for k in keys])
+
+
+def run_cv_jobs(config, jobs, load_subject, save_dir, max_epochs=200, batch_size=64, seed=42, n_folds=5, device=None,
+                resume=True, **fold_kw):
+    """Run ``jobs`` (an iterable of (subject_index, sid, fold): ``shard_jobs(...)`` or a ``JobQueue``) on this process's
+    GPU.  ``load_subject(sid) -> (X (n,C,T) float32, Y (n,))`` NumPy or tensors (``load_subject_train_val`` partial in
+    production); each subject is uploaded once and stays resident while its folds run.  Every finished job leaves
+    ``sub-SID/fold-k-best.pth`` + ``fold-k_history.csv`` + ``fold-k_result.json``; with ``resume`` a job whose result
+    file exists is skipped, so a crashed worker's jobs can simply be re-queued.  Returns the list of result dicts."""
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    cache, done = {}, []
+    for si, sid, k in jobs:
+        sub_dir = os.path.join(save_dir, f"sub-{sid}")
+        os.makedirs(sub_dir, exist_ok=True)
+        res_path = os.path.join(sub_dir, f"fold-{k}_result.json")
+        if resume and os.path.exists(res_path):
+            done.append(json.load(open(res_path)))
+            continue
+        if sid not in cache:
+            cache.clear()                                      # one resident subject at a time per process
+            X, Y = load_subject(sid)
+            cache[sid] = (torch.as_tensor(X).to(dev, non_blocking=True), torch.as_tensor(Y).to(dev, non_blocking=True))
+        X, Y = cache[sid]
+        tr_idx, va_idx = kfold_indices(X.shape[0], n_folds, True, seed)[k]
+        out = train_fold(config, X, Y, tr_idx, va_idx, max_epochs, batch_size, job_seed(seed, n_folds, si, k), **fold_kw)
+        torch.save(out.pop("state_dict"), os.path.join(sub_dir, f"fold-{k}-best.pth"))
+        _write_history(os.path.join(sub_dir, f"fold-{k}_history.csv"), out.pop("history"))
+        res = {"subject": sid, "subject_index": si, "fold": k, **out}
+        tmp = res_path + f".tmp{os.getpid()}"
+        with open(tmp, "w") as f:
+            json.dump(res, f)
+        os.replace(tmp, res_path)                              # the result file appears atomically = the job's commit
+        done.append(res)
+    return done
+
+
+def finalize_cv(config, subjects, save_dir, n_folds=5, test_per_subject=None, device=None):
+    """Host-side join after all ranks finished (train_fast.py:182-240): per subject pick the best fold, save
+    ``best_subject.pth``, predict that subject's test set, write the per-subject and global CSVs.  Returns the
+    summary rows ``[sid, best_val_acc, test_acc, test_f1]``."""
+    from ..models import FAST
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    rows, gp, gt = [], [], []
+    model = None
+    for sid in subjects:
+        sub_dir = os.path.join(save_dir, f"sub-{sid}")
+        folds = []
+        for k in range(n_folds):
+            p = os.path.join(sub_dir, f"fold-{k}_result.json")
+            if os.path.exists(p):
+                folds.append((k, json.load(open(p))["best_val_acc"]))
+        if not folds:
+            continue                                           # "No checkpoint found ... skipping" (train_fast.py:199-201)
+        best_k, best_acc = pick_best_fold(folds)
+        sd = torch.load(os.path.join(sub_dir, f"fold-{best_k}-best.pth"), weights_only=True)
+        torch.save(sd, os.path.join(sub_dir, "best_subject.pth"))
+        test_acc = test_f1 = float("nan")
+        if test_per_subject is not None and sid in test_per_subject:
+            if model is None:
+                model = FAST(config).to(dev)
+            model.load_state_dict(sd)
+            Xt, Yt = test_per_subject[sid]
+            pred = model.predict(torch.as_tensor(Xt).to(dev)).cpu().numpy()
+            true = np.asarray(torch.as_tensor(Yt).cpu()).astype(np.int64)
+            test_acc = float(np.mean(pred == true))
+            test_f1 = macro_f1(true, pred)
+            np.savetxt(os.path.join(sub_dir, "test_predictions.csv"), np.array([pred, true]).T, delimiter=',', fmt='%d',
+                       header='Predicted,True')
+            gp.append(pred); gt.append(true)
+        rows.append([sid, best_acc, test_acc, test_f1])
+        with open(os.path.join(sub_dir, "fold_metrics.csv"), "w", newline="") as f:
+            w = csv.writer(f)
+            w.writerow(["Fold", "Best_Val_Acc"])
+            w.writerows([[k, v] for k, v in folds])
+    with open(os.path.join(save_dir, "summary_per_subject.csv"), "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow(["Subject", "Best_Val_Acc", "Test_Acc", "Test_F1"])
+        w.writerows(rows)
+    if gp:
+        np.savetxt(os.path.join(save_dir, "global_test_predictions.csv"), np.array([np.concatenate(gp), np.concatenate(gt)]).T,
+                   delimiter=',', fmt='%d', header='Predicted,True')
+    return rows
+
+
+def synthetic_subject(subject_index: int, n_trials=350, n_test=50, n_chan=64, n_samples=800, n_classes=5):
+    """SURVEY.md 8d-D4 synthetic subject: ``randn(350,64,800)`` train/val with balanced labels shuffled with seed
+    2000+s, and ``randn(50,64,800)`` test.  Returns ((X, Y), (X_test, Y_test)) as NumPy float32 / uint8."""
+    rng = np.random.default_rng(3000 + subject_index)
+    X = rng.standard_normal((n_trials, n_chan, n_samples), dtype=np.float32)
+    Y = np.repeat(np.arange(n_classes), math.ceil(n_trials / n_classes))[:n_trials].astype(np.uint8)
+    np.random.default_rng(2000 + subject_index).shuffle(Y)
+    Xt = rng.standard_normal((n_test, n_chan, n_samples), dtype=np.float32)
+    Yt = np.repeat(np.arange(n_classes), math.ceil(n_test / n_classes))[:n_test].astype(np.uint8)
+    return (X, Y), (Xt, Yt)

@@ -66,6 +66,7 @@ class FusedTrainer:
             self.lr_by_step = 1
         self.n_sched = self.lr_dev.numel()
         self.steps_done = 0
+        self.grad_scale = 1.0      # dlogits multiplier (a data-parallel run uses 1 / world_size: SUM all-reduce -> global mean)
         n_packed = self.lib.fastb200_head_packed_floats(desc)
         self.packed = torch.empty(n_packed, device=dev)
         self.gpacked = torch.zeros(n_packed, device=dev)
@@ -112,6 +113,11 @@ class FusedTrainer:
 
     # ------------------------------------------------------------------------------------------ launches
     def _launch_train(self, ws):
+        self._launch_grad(ws)
+        self._launch_update()
+
+    def _launch_grad(self, ws):
+        """Everything up to the complete flat gradient in ``self.grad`` (the buffer a data-parallel run all-reduces)."""
         lib, d, p = self.lib, self.desc, N.ptr
         st = N.stream_ptr(self.device)
         B, T, n_win = ws["B"], ws["T"], ws["n_win"]
@@ -121,8 +127,9 @@ class FusedTrainer:
                                       None if self.freeze_head else p(ws["head_saved"]), st), "head_fwd")
         N.check(lib.fastb200_transformer_fwd(d, p(self.flat), p(ws["feat"]), B, n_win, self.mode, p_drop, self.seed, 0,
                                              p(self.step_dev), p(ws["logits"]), p(ws["tr_saved"]), st), "transformer_fwd")
-        N.check(lib.fastb200_ce_fwd_bwd(p(ws["logits"]), p(ws["y"]), ws["y"].element_size(), B, d.n_classes, 1.0,
-                                        p(self.loss), p(ws["dlogits"]), p(ws["pred"]), p(self.n_correct), st), "ce")
+        N.check(lib.fastb200_ce_fwd_bwd(p(ws["logits"]), p(ws["y"]), ws["y"].element_size(), B, d.n_classes,
+                                        self.grad_scale, p(self.loss), p(ws["dlogits"]), p(ws["pred"]), p(self.n_correct), st),
+                "ce")
         self.grad.zero_()
         N.check(lib.fastb200_transformer_bwd(d, p(self.flat), p(ws["feat"]), p(ws["tr_saved"]), p(ws["dlogits"]), B, n_win,
                                              self.mode, p_drop, self.seed, 0, p(self.step_dev), p(self.grad),
@@ -132,6 +139,11 @@ class FusedTrainer:
             N.check(lib.fastb200_head_bwd(d, p(self.packed), p(ws["x"]), p(ws["head_saved"]), p(ws["dfeat"]), B, T, n_win,
                                           d.slide_step, p(self.gpacked), None, st), "head_bwd")
             N.check(lib.fastb200_head_unpack_grad(d, p(self.flat), p(self.gpacked), p(self.grad), st), "head_unpack_grad")
+
+    def _launch_update(self):
+        """AdamW on the flat buffers (lr and step counter read on the device)."""
+        lib, p = self.lib, N.ptr
+        st = N.stream_ptr(self.device)
         N.check(lib.fastb200_adamw_flat(p(self.flat), p(self.grad), p(self.exp_avg), p(self.exp_avg_sq), self.flat.numel(),
                                         p(self.lr_dev), self.lr_by_step, self.betas[0], self.betas[1], self.eps,
                                         self.weight_decay, p(self.step_dev), 1, st), "adamw_flat")
@@ -165,6 +177,12 @@ class FusedTrainer:
     LAUNCHES_TRAIN = 9      # pack, head_fwd, tr_fwd, ce, tr_bwd, head_bwd, unpack, adamw, bump_step
     LAUNCHES_EVAL = 4
 
+    def _phases(self, ws, train):
+        """[(callable, capturable in a CUDA graph)] making up one step, in order."""
+        if not train:
+            return [(lambda: self._launch_eval(ws), True)]
+        return [(lambda: self._launch_train(ws), True)]
+
     def _run(self, x, y, train):
         N.require_cuda(x, "x")
         if x.dtype != torch.float32:
@@ -172,26 +190,36 @@ class FusedTrainer:
         if y.dtype not in (torch.uint8, torch.int64):
             y = y.long()
         ws = self._workspace(x.shape[0], x.shape[2], y.dtype, train)
-        launch = self._launch_train if train else self._launch_eval
+        phases = self._phases(ws, train)
         with torch.cuda.device(self.device):
             ws["x"].copy_(x, non_blocking=True)
             ws["y"].copy_(y.to(self.device, non_blocking=True), non_blocking=True)
             if not self.use_graph:
-                launch(ws)
+                for fn, _ in phases:
+                    fn()
             elif ws["graph"] is None:
                 # one eager run (sets kernel attributes, warms allocators), then capture; capture itself does not
-                # execute, so the eager run IS this step and the graph serves the following ones.
-                launch(ws)
-                g = torch.cuda.CUDAGraph()
+                # execute, so the eager run IS this step and the graphs serve the following ones.  Phases flagged
+                # non-capturable (a collective between two graphs) are kept as plain calls.
+                for fn, _ in phases:
+                    fn()
+                replay = []
                 side = torch.cuda.Stream(self.device)
-                side.wait_stream(torch.cuda.current_stream(self.device))
-                with torch.cuda.stream(side):
-                    with torch.cuda.graph(g, stream=side):
-                        launch(ws)
-                torch.cuda.current_stream(self.device).wait_stream(side)
-                ws["graph"] = g
+                for fn, capturable in phases:
+                    if not capturable:
+                        replay.append(fn)
+                        continue
+                    g = torch.cuda.CUDAGraph()
+                    side.wait_stream(torch.cuda.current_stream(self.device))
+                    with torch.cuda.stream(side):
+                        with torch.cuda.graph(g, stream=side):
+                            fn()
+                    torch.cuda.current_stream(self.device).wait_stream(side)
+                    replay.append(g.replay)
+                ws["graph"] = replay
             else:
-                ws["graph"].replay()
+                for fn in ws["graph"]:
+                    fn()
         return ws
 
     # ------------------------------------------------------------------------------------------ public API

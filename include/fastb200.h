@@ -178,6 +178,20 @@ int fastb200_adamw_flat(float* p, const float* g, float* m, float* v, int64_t n,
                         int lr_by_step, double beta1, double beta2, double eps, double weight_decay,
                         int32_t* step_dev, int bump_step, void* stream);
 
+/*
+ * Data-parallel form of the above for the large-batch config (BASELINE.json configs[4]; the reference itself is
+ * single-device, scripts/train_fast.py:127-131): the all-reduce of the flat gradient is FUSED into the update.
+ * peer_grads: HOST array of n_peers DEVICE pointers, entry r = rank r's flat gradient buffer mapped into this
+ * process (NVLink peer / symmetric memory; entry [own rank] is the local buffer).  Element i of the gradient is
+ * sum_r peer_grads[r][i] in rank order, so all ranks compute bit-identical updates.  The caller orders the launch
+ * after every rank's gradient is complete and keeps the buffers unmodified until every rank's launch finished
+ * (two symmetric-memory barriers on the stream); the kernel itself does no inter-GPU synchronisation.
+ */
+#define FASTB200_MAX_PEERS 16
+int fastb200_adamw_flat_peers(float* p, const float* const* peer_grads, int n_peers, float* m, float* v, int64_t n,
+                              const float* lr_dev, int lr_by_step, double beta1, double beta2, double eps,
+                              double weight_decay, int32_t* step_dev, int bump_step, void* stream);
+
 /* ---- preprocessing that feeds the model ------------------------------------------------------------------ */
 /*
  * Replaces the array math of load_subject_train_val / load_training_set / proc_one
