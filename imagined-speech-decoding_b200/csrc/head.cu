@@ -475,6 +475,195 @@ __global__ void __launch_bounds__(HEAD_THREADS, 1) head_bwd_kernel(const __grid_
     flush(cur_z);
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// backward, tensor-core split: everything except the cnn3 / cnn4 weight gradients (those are head_wgrad_tc.cu)
+// ---------------------------------------------------------------------------------------------------------
+// Same chain as head_bwd_kernel, restructured so that no global-memory latency is exposed inside an item:
+//   * y4 of the NEXT item arrives by one bulk async copy (TMA engine) into its own buffer while this item computes;
+//   * the zone's electrodes of this window are gathered with 4-byte cp.async (the trial rows are only 4-byte aligned)
+//     issued at the top of the item and awaited just before the embed weight-gradient phase;
+//   * dL/dy4 and dL/dy3 are written to `dys` ([F][TS] each) for the tensor-core weight-gradient kernel.
+struct HeadDgradArgs {
+    HeadGeom g;
+    const float* packed;
+    const float* x;
+    const float* saved;
+    const float* dfeat;
+    float* gpacked;
+    float* dx;
+    float* dys;
+    int B, T, n_win, step;
+    int RS, TS, T_out, n_tt;
+    int items_per_cta, n_items;
+};
+
+template <int F>
+__global__ void __launch_bounds__(HEAD_THREADS, 1) head_dgrad_kernel(const __grid_constant__ HeadDgradArgs a) {
+    extern __shared__ __align__(128) float smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int RS = a.RS, T_out = a.T_out, TS = a.TS;
+    float* bufA = smem;
+    float* bufB = bufA + F * RS;                     // gathered electrodes (up to 32 rows)
+    float* bufC = bufB + 32 * RS;
+    float* y4s = bufC + F * RS;                      // [F][TS] y4 of the current item (bulk copy target)
+    float* w3t = y4s + F * TS;
+    float* w4t = w3t + F * TAPS * F;
+    float* dfs = w4t + F * TAPS * F;
+    uint64_t* bar = reinterpret_cast<uint64_t*>(dfs + round_up(F, 4));     // [0] weights, [1] y4
+
+    const int BN = a.B * a.n_win;
+    const int first = blockIdx.x * a.items_per_cta;
+    const int last = min(first + a.items_per_cta, a.n_items);
+    if (first >= last) return;
+
+    float accE[4][TAPS], accb[4];
+    int cur_z = -1;
+    uint32_t parity_w = 0, parity_y = 0;
+    const int co0 = warp * 4;
+    const float inv_T = 1.0f / (float)T_out;
+    const size_t item_sz = (size_t)F * TS;
+    const uint32_t y_bytes = (uint32_t)(item_sz * sizeof(float));
+
+    auto fwd_item = [&](int idx) -> size_t {
+        const int z = idx / BN, bn = idx - z * BN;
+        return (size_t)bn * a.g.Z + z;
+    };
+    if (tid == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+        fence_mbar_init();
+        mbar_expect_tx(&bar[1], y_bytes);
+        bulk_g2s(y4s, a.saved + fwd_item(first) * 3 * item_sz + 2 * item_sz, y_bytes, &bar[1]);
+    }
+    // pad columns of the conv operand buffers are zero for the whole kernel (the phases only write columns [2, 2 + 128 n_tt))
+    for (int i = tid; i < F * RS; i += HEAD_THREADS) { bufA[i] = 0.f; bufC[i] = 0.f; }
+    __syncthreads();
+
+    auto flush = [&](int z) {
+        const int Cz = a.g.cz[z];
+        float* gz = a.gpacked + a.g.pk[z];
+        if (co0 < F) {
+            if (lane < Cz) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int k = 0; k < TAPS; ++k) atomicAdd(gz + (lane * TAPS + k) * F + co0 + i, accE[i][k]);
+            }
+            if (lane == 0) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) atomicAdd(gz + pz_beff(Cz, F) + co0 + i, accb[i]);
+            }
+        }
+    };
+
+    for (int idx = first; idx < last; ++idx) {
+        const int z = idx / BN, bn = idx - z * BN;
+        const int b = bn / a.n_win, n = bn - b * a.n_win;
+        const int Cz = a.g.cz[z];
+        const size_t item = (size_t)bn * a.g.Z + z;
+        if (z != cur_z) {
+            if (cur_z >= 0) flush(cur_z);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                accb[i] = 0.f;
+#pragma unroll
+                for (int k = 0; k < TAPS; ++k) accE[i][k] = 0.f;
+            }
+            __syncthreads();
+            if (tid == 0) {
+                const float* pz = a.packed + a.g.pk[z];
+                const uint32_t b_w = (uint32_t)(F * TAPS * F) * 4u;
+                fence_proxy_async();
+                mbar_expect_tx(&bar[0], 2 * b_w);
+                bulk_g2s(w3t, pz + pz_w3(Cz, F) + 2 * F * TAPS * F, b_w, &bar[0]);
+                bulk_g2s(w4t, pz + pz_w3(Cz, F) + 3 * F * TAPS * F, b_w, &bar[0]);
+            }
+            mbar_wait(&bar[0], parity_w);
+            parity_w ^= 1;
+            cur_z = z;
+        }
+        // electrodes of this window -> B (column 2 + t'), asynchronously; awaited before Q5
+        {
+            const int* chan = a.g.chan + a.g.zoff[z];
+            const float* xb = a.x + (size_t)b * a.g.C * a.T + (size_t)n * a.step;
+            const uint32_t dst0 = smem_u32(bufB);
+            for (int i = tid; i < Cz * RS; i += HEAD_THREADS) {
+                const int c = i / RS, t2 = i - c * RS - 2;
+                const bool ok = t2 >= 0 && t2 < a.g.W;
+                const float* src = ok ? xb + (size_t)chan[c] * a.T + t2 : a.x;
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst0 + 4u * i), "l"(src), "r"(ok ? 4u : 0u) : "memory");
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        }
+        float* dy = a.dys + item * 2 * item_sz;
+        if (tid < F) dfs[tid] = __ldg(a.dfeat + item * F + tid) * inv_T;
+        mbar_wait(&bar[1], parity_y);
+        parity_y ^= 1;
+        __syncthreads();
+        // Q0: A <- dL/dy4 = dfeat / T * gelu'(y4) (column 2 + t), also written to dys[0]
+        for (int i = tid; i < F * (TS / 4); i += HEAD_THREADS) {
+            const int f = i / (TS / 4), t = (i - f * (TS / 4)) * 4;
+            const float4 y = *reinterpret_cast<const float4*>(y4s + f * TS + t);
+            const float d = dfs[f];
+            float4 g;
+            g.x = t + 0 < T_out ? d * gelu_grad_f(y.x) : 0.f;
+            g.y = t + 1 < T_out ? d * gelu_grad_f(y.y) : 0.f;
+            g.z = t + 2 < T_out ? d * gelu_grad_f(y.z) : 0.f;
+            g.w = t + 3 < T_out ? d * gelu_grad_f(y.w) : 0.f;
+            *reinterpret_cast<float4*>(dy + f * TS + t) = g;
+            float* o = bufA + f * RS + 2 + t;
+            *reinterpret_cast<float2*>(o) = make_float2(g.x, g.y);
+            *reinterpret_cast<float2*>(o + 2) = make_float2(g.z, g.w);
+        }
+        // columns [2 + TS, 2 + 128 n_tt) of A are rewritten by Q3 of the previous item with masked (zero) values
+        __syncthreads();
+        if (tid == 0 && idx + 1 < last) {              // y4 buffer is free: fetch the next item's
+            fence_proxy_async();
+            mbar_expect_tx(&bar[1], y_bytes);
+            bulk_g2s(y4s, a.saved + fwd_item(idx + 1) * 3 * item_sz + 2 * item_sz, y_bytes, &bar[1]);
+        }
+        // Q1: C <- dL/dy3 = conv(dy4, flipped cnn4^T), also written to dys[1]
+        conv_phase<F, EPI_STORE>(bufA, F, w4t, nullptr, bufC, dy + item_sz, nullptr, RS, TS, T_out, a.n_tt);
+        __syncthreads();
+        // Q3: A <- dL/dy2 = conv(dy3, flipped cnn3^T)
+        conv_phase<F, EPI_STORE>(bufC, F, w3t, nullptr, bufA, nullptr, nullptr, RS, TS, T_out, a.n_tt);
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncthreads();
+        // Q5: dWeff += dy2 (x) x ; dbeff += sum_t dy2 ; optional dx
+        wgrad_phase<F>(bufA, bufB, Cz, accE, RS, T_out);
+        if (co0 < F) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                float s = 0.f;
+                for (int col = 2 + lane; col < 2 + T_out; col += 32) s += bufA[(co0 + i) * RS + col];
+                s = warp_sum(s);
+                accb[i] += s;
+            }
+        }
+        if (a.dx != nullptr) {
+            const int* chan = a.g.chan + a.g.zoff[z];
+            const float* weff = a.packed + a.g.pk[z];
+            float* dxb = a.dx + (size_t)b * a.g.C * a.T + (size_t)n * a.step;
+            for (int i = tid; i < Cz * a.g.W; i += HEAD_THREADS) {
+                const int c = i / a.g.W, tp = i - c * a.g.W;
+                float s = 0.f;
+#pragma unroll
+                for (int k = 0; k < TAPS; ++k) {
+                    const int t = tp - k;
+                    if (t >= 0 && t < T_out) {
+                        const float* wk = weff + (c * TAPS + k) * F;
+                        for (int f = 0; f < F; ++f) s = fmaf(__ldg(wk + f), bufA[f * RS + 2 + t], s);
+                    }
+                }
+                atomicAdd(dxb + (size_t)chan[c] * a.T + tp, s);
+            }
+        }
+        __syncthreads();
+    }
+    flush(cur_z);
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // stand-alone index kernel (parity / diagnostics; the fused path never materialises this tensor)
 // ---------------------------------------------------------------------------------------------------------
@@ -610,6 +799,37 @@ extern "C" int fastb200_head_bwd(const fastb200_model* m, const float* packed, c
     if (F == 32) { LAUNCH_BWD(32) } else if (F == 16) { LAUNCH_BWD(16) } else { LAUNCH_BWD(8) }
 #undef LAUNCH_BWD
     return check_launch("head_bwd");
+}
+
+int fb::head_dgrad_launch(const fastb200_model* m, const float* packed, const float* x, const float* saved,
+                          const float* dfeat, int B, int T, int n_win, int step, float* gpacked, float* dx, float* dys,
+                          void* stream) {
+    if (int r = validate_model(m)) return r;
+    FB_REQUIRE(B >= 0 && n_win >= 1 && step >= 1, "bad B/n_win/step");
+    FB_REQUIRE(saved != nullptr && dys != nullptr, "head_dgrad needs the saved activations and the dys workspace");
+    if (B == 0) return 0;
+    const int F = m->dim_cnn, W = m->window_len;
+    HeadDgradArgs a;
+    a.g = make_geom(*m);
+    a.packed = packed; a.x = x; a.saved = saved; a.dfeat = dfeat; a.gpacked = gpacked; a.dx = dx; a.dys = dys;
+    a.B = B; a.T = T; a.n_win = n_win; a.step = step;
+    a.TS = head_saved_stride(W); a.T_out = head_t_out(W); a.n_tt = head_n_tt(W);
+    a.RS = a.n_tt * 128 + 36;
+    const int64_t items = (int64_t)B * n_win * m->n_zones;
+    FB_REQUIRE(items < (1ll << 31), "too many items for one launch");
+    a.n_items = (int)items;
+    int grid = (int)(items < NUM_SMS ? items : NUM_SMS);
+    a.items_per_cta = ceil_div((int)items, grid);
+    grid = ceil_div((int)items, a.items_per_cta);
+    const size_t smem = (size_t)((2 * F + 32) * a.RS + F * a.TS + 2 * F * TAPS * F + round_up(F, 4) + 8) * sizeof(float);
+    FB_REQUIRE(smem <= 227 * 1024, "window_len=%d too long for the shared-memory resident backward", W);
+    int r = 0;
+#define LAUNCH_DG(FF)                                                                      \
+    if ((r = set_smem(head_dgrad_kernel<FF>, smem))) return r;                              \
+    head_dgrad_kernel<FF><<<grid, HEAD_THREADS, smem, as_stream(stream)>>>(a);
+    if (F == 32) { LAUNCH_DG(32) } else if (F == 16) { LAUNCH_DG(16) } else { LAUNCH_DG(8) }
+#undef LAUNCH_DG
+    return check_launch("head_dgrad");
 }
 
 extern "C" int fastb200_window_gather(const float* x, const int32_t* chan, float* out, int B, int C, int T, int W,

@@ -25,7 +25,7 @@ import torch.nn.functional as F
 from .. import _native as N
 
 __all__ = ["FAST", "AttentionBlock", "CVBlock", "Conv4Layers", "EEGNet_Encoder", "HeadConv_Paper_Version", "Head",
-           "set_head_precision", "get_head_precision"]
+           "set_head_precision", "get_head_precision", "set_head_backward", "get_head_backward"]
 
 # Arithmetic of the Conv4Layers head when no gradient is needed (inference):
 #   'bf16x3'  tcgen05 tensor cores, every fp32 operand split into 3 bf16 terms (24 mantissa bits, fp32-equivalent)
@@ -50,6 +50,28 @@ def set_head_precision(mode: str):
 
 def get_head_precision() -> str:
     return _HEAD_PRECISION
+
+
+# Where the cnn3 / cnn4 weight gradients of the head backward are computed:
+#   'tc'    tcgen05 tensor cores (fastb200_head_bwd_tc: split-bf16 operands, fp32 accumulation in TMEM) for the shapes it
+#           supports, the CUDA-core kernel otherwise
+#   'ffma'  CUDA-core kernel only (fastb200_head_bwd)
+_HEAD_BACKWARD = os.environ.get("FASTB200_HEAD_BWD", "tc")
+
+
+def set_head_backward(mode: str):
+    global _HEAD_BACKWARD
+    if mode not in ("tc", "ffma"):
+        raise ValueError(f"head backward must be 'tc' or 'ffma', got {mode!r}")
+    _HEAD_BACKWARD = mode
+
+
+def get_head_backward() -> str:
+    return _HEAD_BACKWARD
+
+
+def head_bwd_uses_tc(desc) -> bool:
+    return _HEAD_BACKWARD == "tc" and bool(N.lib().fastb200_head_bwd_tc_supported(desc))
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -210,8 +232,13 @@ class _HeadFn(torch.autograd.Function):
             st = N.stream_ptr(xin.device)
             gpacked = torch.zeros_like(ctx.packed)
             dx = torch.zeros_like(xin) if need_dx else None
-            N.check(lib.fastb200_head_bwd(desc, N.ptr(ctx.packed), N.ptr(xin), N.ptr(ctx.saved), N.ptr(dfeat), B, T,
-                                          ctx.n_win, ctx.step, N.ptr(gpacked), N.ptr(dx), st), "head_bwd")
+            if head_bwd_uses_tc(desc):
+                work = torch.empty(lib.fastb200_head_bwd_tc_work_floats(desc, B, ctx.n_win), device=xin.device, dtype=torch.float32)
+                N.check(lib.fastb200_head_bwd_tc(desc, N.ptr(ctx.packed), N.ptr(xin), N.ptr(ctx.saved), N.ptr(dfeat), B, T,
+                                                 ctx.n_win, ctx.step, N.ptr(gpacked), N.ptr(dx), N.ptr(work), st), "head_bwd_tc")
+            else:
+                N.check(lib.fastb200_head_bwd(desc, N.ptr(ctx.packed), N.ptr(xin), N.ptr(ctx.saved), N.ptr(dfeat), B, T,
+                                              ctx.n_win, ctx.step, N.ptr(gpacked), N.ptr(dx), st), "head_bwd")
             gflat = torch.empty_like(flat)
             N.check(lib.fastb200_head_unpack_grad(desc, N.ptr(flat), N.ptr(gpacked), N.ptr(gflat), st), "head_unpack_grad")
         grads = []

@@ -91,7 +91,7 @@ class FusedTrainer:
     # ------------------------------------------------------------------------------------------ workspaces
     def _workspace(self, B, T, label_dtype, train):
         from ..models import fast as FM
-        key = (B, T, label_dtype, train, None if train else FM.get_head_precision())   # a captured graph bakes the kernel choice in
+        key = (B, T, label_dtype, train, FM.get_head_backward() if train else FM.get_head_precision())   # a captured graph bakes the kernel choice in
         ws = self._ws.get(key)
         if ws is not None:
             return ws
@@ -108,6 +108,10 @@ class FusedTrainer:
             ws["tr_saved"] = torch.empty(max(1, lib.fastb200_transformer_saved_floats(d, B, n_win)), device=dev)
             ws["dlogits"] = torch.empty(B, d.n_classes, device=dev)
             ws["dfeat"] = torch.empty_like(ws["feat"])
+            from ..models import fast as FM
+            ws["bwd_work"] = None
+            if FM.head_bwd_uses_tc(d):
+                ws["bwd_work"] = torch.empty(lib.fastb200_head_bwd_tc_work_floats(d, B, n_win), device=dev)
         self._ws[key] = ws
         return ws
 
@@ -136,8 +140,12 @@ class FusedTrainer:
                                              None if self.freeze_head else p(ws["dfeat"]), st), "transformer_bwd")
         if not self.freeze_head:
             self.gpacked.zero_()
-            N.check(lib.fastb200_head_bwd(d, p(self.packed), p(ws["x"]), p(ws["head_saved"]), p(ws["dfeat"]), B, T, n_win,
-                                          d.slide_step, p(self.gpacked), None, st), "head_bwd")
+            if ws["bwd_work"] is not None:
+                N.check(lib.fastb200_head_bwd_tc(d, p(self.packed), p(ws["x"]), p(ws["head_saved"]), p(ws["dfeat"]), B, T, n_win,
+                                                 d.slide_step, p(self.gpacked), None, p(ws["bwd_work"]), st), "head_bwd_tc")
+            else:
+                N.check(lib.fastb200_head_bwd(d, p(self.packed), p(ws["x"]), p(ws["head_saved"]), p(ws["dfeat"]), B, T, n_win,
+                                              d.slide_step, p(self.gpacked), None, st), "head_bwd")
             N.check(lib.fastb200_head_unpack_grad(d, p(self.flat), p(self.gpacked), p(self.grad), st), "head_unpack_grad")
 
     def _launch_update(self):

@@ -132,6 +132,21 @@ int fastb200_head_pack_tc(const fastb200_model* m, const float* params, void* pa
 int fastb200_head_fwd_tc(const fastb200_model* m, const void* packed, const float* x, int B, int T, int n_win,
                          int step, float* feat, int n_terms, void* stream);
 
+/* ---- zone embedding head backward with the cnn3 / cnn4 weight gradients on the tensor cores ------------------- */
+/*
+ * Same function and arguments as fastb200_head_bwd (autograd of fast.py:111-119, 210, 247-251), split in two launches:
+ * the CUDA-core kernel computes the input gradients of cnn4 / cnn3, the collapsed-embed weight / bias gradients and the
+ * optional dx, and WRITES dL/dy4, dL/dy3 to `work`; a tcgen05 kernel then forms the cnn3 / cnn4 weight gradients
+ * (per tap a (32 x T) x (T x 32) contraction over time, split-bf16 operands, fp32 accumulation in TMEM across all items).
+ * Shapes supported: dim_cnn == 32, 20 <= window_len <= 260 (fastb200_head_bwd_tc_supported() returns 1).
+ *   work: fastb200_head_bwd_tc_work_floats(m, B, n_win) floats (B*n_win*Z items x 2 x F x roundup4(W-4)).
+ */
+int     fastb200_head_bwd_tc_supported(const fastb200_model* m);
+int64_t fastb200_head_bwd_tc_work_floats(const fastb200_model* m, int B, int n_win);
+int fastb200_head_bwd_tc(const fastb200_model* m, const float* packed, const float* x, const float* saved,
+                         const float* dfeat, int B, int T, int n_win, int step, float* gpacked, float* dx,
+                         float* work, void* stream);
+
 /* ---- transformer (input_layer, CLS, pos, L x AttentionBlock, last_layer) --------------------------------- */
 /* Floats saved per forward for the backward: B * (n_layers + 1) * n_tok * D  (block inputs + final tokens). */
 int64_t fastb200_transformer_saved_floats(const fastb200_model* m, int B, int n_win);

@@ -122,7 +122,17 @@ def test_prod_forward(golden):
         assert torch.equal(m.batched_forward_head(x, 125, 1), m.forward_head(x, 125))
 
 
-def test_prod_backward(golden):
+@pytest.fixture
+def head_backward():
+    from fast.models import fast as FM
+    old = FM.get_head_backward()
+    yield FM.set_head_backward
+    FM.set_head_backward(old)
+
+
+@pytest.mark.parametrize("bwd", ["ffma", "tc"])
+def test_prod_backward(golden, head_backward, bwd):
+    head_backward(bwd)
     m = _prod_model().eval()                                      # golden gradients were taken in eval mode
     x = _prod_x().cuda().requires_grad_(True)
     y = torch.from_numpy(golden["prod/y"]).cuda()
@@ -145,8 +155,10 @@ def test_prod_backward(golden):
     assert abs(dfp[3] - golden["prod/dx_fp"][3]) / golden["prod/dx_fp"][3] < 1e-3
 
 
-def test_prod_backward_vs_oracle_all_tensors():
+@pytest.mark.parametrize("bwd", ["ffma", "tc"])
+def test_prod_backward_vs_oracle_all_tensors(head_backward, bwd):
     """Every one of the 94 gradient tensors against the oracle's autograd on a fresh input (not only the golden subset)."""
+    head_backward(bwd)
     m = _prod_model().eval()
     sd = {k: v.detach().cpu() for k, v in m.state_dict().items()}
     g = torch.Generator().manual_seed(77)
@@ -503,3 +515,23 @@ def test_tc_head_zone_sizes_and_fallback(head_precision):
         with torch.no_grad():
             f = m.forward_head(x.cuda())
         assert rel_err(f, _oracle_feat64(m, cfg, x)) < TC_TOL["bf16x3"]
+
+
+def test_head_bwd_tc_weight_gradients_vs_ffma_at_scale(head_backward):
+    """cnn3 / cnn4 weight gradients from the tcgen05 kernel against the CUDA-core kernel on a batch large enough that every
+    persistent CTA walks many items (TMEM accumulation across items, staging ring and tile double-buffer wrap-around)."""
+    m = _prod_model(dropout=0.0).train()
+    g = torch.Generator().manual_seed(5)
+    x = (torch.randn(96, 64, 795, generator=g) * 4.0).cuda()
+    y = torch.randint(0, 5, (96,), generator=g).cuda()
+    grads = {}
+    for bwd in ("ffma", "tc"):
+        head_backward(bwd)
+        m.zero_grad(set_to_none=True)
+        torch.nn.CrossEntropyLoss()(m(x), y).backward()
+        grads[bwd] = {k: p.grad.clone() for k, p in m.named_parameters()}
+    for k in grads["ffma"]:
+        e = rel_err(grads["tc"][k], grads["ffma"][k])
+        assert e < (TOL if "cnn3" in k or "cnn4" in k else 1e-5), (k, e)
+    worst = max(rel_err(grads["tc"][k], grads["ffma"][k]) for k in grads["tc"] if "cnn3" in k or "cnn4" in k)
+    print("worst cnn3/cnn4 weight-gradient deviation tc vs ffma:", worst)
