@@ -107,6 +107,8 @@ struct FwdArgs {
     const uint8_t* packed;
     const float* x;
     float* feat;
+    float* saved;                              // SAVE builds (training forward): per item 3 x [F][TS] fp32 y2, y3, y4, as head_fwd writes them
+    int TS;
     long long* prof;                           // PROF builds only: per-CTA wait-cycle counters [grid][16]
     int dbg;                                   // PROF builds only: bit0 skip operand stores, bit1 skip GELU, bit2 skip electrode loads
     int B, T, n_win, step, C, W, Z;
@@ -134,7 +136,7 @@ constexpr int SMEM_HDR = 3072;                 // bytes reserved for Smem in fro
 static_assert(sizeof(Smem) <= SMEM_HDR, "Smem header overflows its reservation");
 
 // ---- forward kernel --------------------------------------------------------------------------------------------------
-template <int NT, bool PROF>
+template <int NT, bool PROF, bool SAVE>
 __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_constant__ FwdArgs a) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
@@ -380,6 +382,15 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
                 }
         };
         // v (+ bias) -> masked -> bf16 terms -> this item's operand tile; signals `ready`
+        // training forward: row t of stage `stage` (0: y2, 1: y3, 2: y4) of this item, columns [CW h, CW h + CW) -- each row is
+        // written by the stream that owns it (both streams hold valid values there, see the halo argument in the header)
+        auto save_rows = [&](const float (&v)[CW], bool add_bias, int it, int stage) {
+            if (!own) return;
+            const size_t item = (size_t)(rank + it * nz) * a.Z + z;
+            float* dst = a.saved + (item * 3 + stage) * (size_t)(F * a.TS) + (size_t)(CW * h) * a.TS + t;
+#pragma unroll
+            for (int i = 0; i < CW; ++i) dst[(size_t)i * a.TS] = add_bias ? v[i] + beff[i] : v[i];
+        };
         auto to_operand = [&](float (&v)[CW], bool add_bias, int it, uint64_t* ready) {
             uint8_t* yt = yt0 + (it & 1) * y_bytes(NT);
             if (!(PROF && (a.dbg & 1)))
@@ -410,6 +421,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
             float v[CW];
             drain(lane_addr + (2 + s) * DCOLS, v);
             to_operand(v, true, it, &sm.ye_ready[s]);
+            if (SAVE) save_rows(v, true, it, 0);
             if (PROF) ep[0] += clock64() - c0;
         };
         auto epi_cnn3 = [&](int it) {
@@ -421,6 +433,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
             float v[CW];
             drain(lane_addr + s * DCOLS, v);
             to_operand(v, false, it, &sm.yc_ready[s]);
+            if (SAVE) save_rows(v, false, it, 1);
             if (PROF) ep[1] += clock64() - c0;
         };
         auto epi_cnn4 = [&](int it) {
@@ -433,6 +446,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
             drain(lane_addr + s * DCOLS, v);
             tc_fence_before();
             mbar_arrive(&sm.d_free[s]);                             // accumulator drained: next item's cnn3 may overwrite it
+            if (SAVE) save_rows(v, false, it, 2);
 #pragma unroll
             for (int i = 0; i < CW; i += 2) {
                 v[i] = own ? v[i] : 0.f;                            // gelu(0) == 0: rows this stream does not own add nothing
@@ -530,8 +544,8 @@ extern "C" int fastb200_head_pack_tc(const fastb200_model* m, const float* param
 static thread_local long long* g_tc_prof = nullptr;
 extern "C" void fastb200_debug_set_tc_profile(long long* dev_buf) { g_tc_prof = dev_buf; }
 
-extern "C" int fastb200_head_fwd_tc(const fastb200_model* m, const void* packed, const float* x, int B, int T, int n_win,
-                                    int step, float* feat, int n_terms, void* stream) {
+static int head_fwd_tc_launch(const fastb200_model* m, const void* packed, const float* x, int B, int T, int n_win,
+                              int step, float* feat, float* saved, int n_terms, void* stream) {
     if (int r = tc_supported(m, n_terms)) return r;
     FB_REQUIRE(B >= 0 && n_win >= 1 && step >= 1, "bad B/n_win/step");
     FB_REQUIRE((n_win - 1) * (int64_t)step + m->window_len <= T, "windows run past the trial: n_win=%d step=%d W=%d T=%d", n_win, step, m->window_len, T);
@@ -539,6 +553,7 @@ extern "C" int fastb200_head_fwd_tc(const fastb200_model* m, const void* packed,
     if (B == 0) return 0;
     tc::FwdArgs a;
     a.packed = static_cast<const uint8_t*>(packed); a.x = x; a.feat = feat; a.prof = g_tc_prof;
+    a.saved = saved; a.TS = head_saved_stride(m->window_len);
     a.dbg = (g_tc_prof && getenv("FASTB200_TC_DBG")) ? atoi(getenv("FASTB200_TC_DBG")) : 0;
     a.B = B; a.T = T; a.n_win = n_win; a.step = step; a.C = m->n_chan; a.W = m->window_len; a.Z = m->n_zones;
     a.T_out = m->window_len - 4; a.split = a.T_out / 2; a.tb1 = a.T_out - 128;
@@ -578,12 +593,24 @@ extern "C" int fastb200_head_fwd_tc(const fastb200_model* m, const void* packed,
     const size_t smem = tc::SMEM_HDR + tc::zone_bytes(n_terms) + 2 * tc::x_bytes(n_terms) + 4 * tc::y_bytes(n_terms) +
                         2 * tc::stg_tiles(n_terms) * tc::STG_BYTES;
     cudaError_t e;
-#define LAUNCH_TC(NTT, PROFF)                                                                                      \
-    e = cudaFuncSetAttribute(tc::head_fwd_tc_kernel<NTT, PROFF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+#define LAUNCH_TC(NTT, PROFF, SAVEE)                                                                               \
+    e = cudaFuncSetAttribute(tc::head_fwd_tc_kernel<NTT, PROFF, SAVEE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
     if (e != cudaSuccess) return fail((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));                 \
-    tc::head_fwd_tc_kernel<NTT, PROFF><<<grid, tc::THREADS, smem, as_stream(stream)>>>(a);
-    if (a.prof) { if (n_terms == 2) { LAUNCH_TC(2, true) } else { LAUNCH_TC(3, true) } }
-    else        { if (n_terms == 2) { LAUNCH_TC(2, false) } else { LAUNCH_TC(3, false) } }
+    tc::head_fwd_tc_kernel<NTT, PROFF, SAVEE><<<grid, tc::THREADS, smem, as_stream(stream)>>>(a);
+    if (saved)       { if (n_terms == 2) { LAUNCH_TC(2, false, true) } else { LAUNCH_TC(3, false, true) } }
+    else if (a.prof) { if (n_terms == 2) { LAUNCH_TC(2, true, false) } else { LAUNCH_TC(3, true, false) } }
+    else             { if (n_terms == 2) { LAUNCH_TC(2, false, false) } else { LAUNCH_TC(3, false, false) } }
 #undef LAUNCH_TC
     return check_launch("head_fwd_tc");
+}
+
+extern "C" int fastb200_head_fwd_tc(const fastb200_model* m, const void* packed, const float* x, int B, int T, int n_win,
+                                    int step, float* feat, int n_terms, void* stream) {
+    return head_fwd_tc_launch(m, packed, x, B, T, n_win, step, feat, nullptr, n_terms, stream);
+}
+
+extern "C" int fastb200_head_fwd_tc_train(const fastb200_model* m, const void* packed, const float* x, int B, int T, int n_win,
+                                          int step, float* feat, float* saved, int n_terms, void* stream) {
+    FB_REQUIRE(saved != nullptr, "head_fwd_tc_train needs the activation workspace (fastb200_head_saved_floats)");
+    return head_fwd_tc_launch(m, packed, x, B, T, n_win, step, feat, saved, n_terms, stream);
 }

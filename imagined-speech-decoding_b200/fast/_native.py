@@ -61,6 +61,7 @@ SIGNATURES = {
     "fastb200_head_packed_tc_bytes": (C.c_int64, [_MP, C.c_int]),
     "fastb200_head_pack_tc": (C.c_int, [_MP, _P, _P, C.c_int, _P]),
     "fastb200_head_fwd_tc": (C.c_int, [_MP, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, C.c_int, _P]),
+    "fastb200_head_fwd_tc_train": (C.c_int, [_MP, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P, C.c_int, _P]),
     "fastb200_transformer_saved_floats": (C.c_int64, [_MP, C.c_int, C.c_int]),
     "fastb200_transformer_fwd": (C.c_int, [_MP, _P, _P, C.c_int, C.c_int, C.c_int, C.c_float, C.c_uint64, C.c_uint64,
                                            _P, _P, _P, _P]),

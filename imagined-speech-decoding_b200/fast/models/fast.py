@@ -214,8 +214,15 @@ class _HeadFn(torch.autograd.Function):
             saved = None
             if need_grad:
                 saved = torch.empty(lib.fastb200_head_saved_floats(desc, B, n_win), device=xin.device, dtype=torch.float32)
-            N.check(lib.fastb200_head_fwd(desc, N.ptr(packed), N.ptr(xin), B, T, n_win, step, N.ptr(feat), N.ptr(saved), st),
-                    "head_fwd")
+            if need_grad and n_terms and lib.fastb200_head_tc_supported(desc):
+                # training: tensor-core forward that also writes y2 / y3 / y4 for the backward kernels
+                packed_tc = torch.empty(lib.fastb200_head_packed_tc_bytes(desc, n_terms), device=xin.device, dtype=torch.uint8)
+                N.check(lib.fastb200_head_pack_tc(desc, N.ptr(flat), N.ptr(packed_tc), n_terms, st), "head_pack_tc")
+                N.check(lib.fastb200_head_fwd_tc_train(desc, N.ptr(packed_tc), N.ptr(xin), B, T, n_win, step, N.ptr(feat),
+                                                       N.ptr(saved), n_terms, st), "head_fwd_tc_train")
+            else:
+                N.check(lib.fastb200_head_fwd(desc, N.ptr(packed), N.ptr(xin), B, T, n_win, step, N.ptr(feat), N.ptr(saved), st),
+                        "head_fwd")
         ctx.desc, ctx.flat, ctx.offsets, ctx.step, ctx.n_win = desc, flat, offsets, step, n_win
         ctx.xin, ctx.packed, ctx.saved = xin, packed, saved
         ctx.shapes = [p.shape for p in params]

@@ -91,13 +91,14 @@ class FusedTrainer:
     # ------------------------------------------------------------------------------------------ workspaces
     def _workspace(self, B, T, label_dtype, train):
         from ..models import fast as FM
-        key = (B, T, label_dtype, train, FM.get_head_backward() if train else FM.get_head_precision())   # a captured graph bakes the kernel choice in
+        key = (B, T, label_dtype, train, FM.get_head_backward() if train else None, FM.get_head_precision())   # a captured graph bakes the kernel choice in
         ws = self._ws.get(key)
         if ws is not None:
             return ws
         d, dev, lib = self.desc, self.device, self.lib
         n_win = (T - d.window_len) // d.slide_step + 1
-        ws = dict(B=B, T=T, n_win=n_win, graph=None,
+        n_terms = FM._TERMS[FM.get_head_precision()]
+        ws = dict(B=B, T=T, n_win=n_win, graph=None, fwd_terms=n_terms if (n_terms and lib.fastb200_head_tc_supported(d)) else 0,
                   x=torch.empty(B, d.n_chan, T, device=dev),
                   y=torch.empty(B, device=dev, dtype=label_dtype),
                   feat=torch.empty(B, n_win, d.n_zones, d.dim_cnn, device=dev),
@@ -115,6 +116,13 @@ class FusedTrainer:
         self._ws[key] = ws
         return ws
 
+    def _packed_tc(self, n_terms):
+        key = ("packed_tc", n_terms)
+        if key not in self._ws:
+            self._ws[key] = torch.empty(self.lib.fastb200_head_packed_tc_bytes(self.desc, n_terms), device=self.device,
+                                        dtype=torch.uint8)
+        return self._ws[key]
+
     # ------------------------------------------------------------------------------------------ launches
     def _launch_train(self, ws):
         self._launch_grad(ws)
@@ -127,8 +135,20 @@ class FusedTrainer:
         B, T, n_win = ws["B"], ws["T"], ws["n_win"]
         p_drop = float(self.model._p_drop) if (self.model.training and self.mode == N.MODE_DEFAULT) else 0.0
         N.check(lib.fastb200_head_pack(d, p(self.flat), p(self.packed), st), "head_pack")
-        N.check(lib.fastb200_head_fwd(d, p(self.packed), p(ws["x"]), B, T, n_win, d.slide_step, p(ws["feat"]),
-                                      None if self.freeze_head else p(ws["head_saved"]), st), "head_fwd")
+        n_terms = ws["fwd_terms"]
+        if n_terms:
+            # tensor-core forward; in training form it also writes y2 / y3 / y4 for the backward kernels
+            pk = self._packed_tc(n_terms)
+            N.check(lib.fastb200_head_pack_tc(d, p(self.flat), p(pk), n_terms, st), "head_pack_tc")
+            if self.freeze_head:
+                N.check(lib.fastb200_head_fwd_tc(d, p(pk), p(ws["x"]), B, T, n_win, d.slide_step, p(ws["feat"]), n_terms, st),
+                        "head_fwd_tc")
+            else:
+                N.check(lib.fastb200_head_fwd_tc_train(d, p(pk), p(ws["x"]), B, T, n_win, d.slide_step, p(ws["feat"]),
+                                                       p(ws["head_saved"]), n_terms, st), "head_fwd_tc_train")
+        else:
+            N.check(lib.fastb200_head_fwd(d, p(self.packed), p(ws["x"]), B, T, n_win, d.slide_step, p(ws["feat"]),
+                                          None if self.freeze_head else p(ws["head_saved"]), st), "head_fwd")
         N.check(lib.fastb200_transformer_fwd(d, p(self.flat), p(ws["feat"]), B, n_win, self.mode, p_drop, self.seed, 0,
                                              p(self.step_dev), p(ws["logits"]), p(ws["tr_saved"]), st), "transformer_fwd")
         N.check(lib.fastb200_ce_fwd_bwd(p(ws["logits"]), p(ws["y"]), ws["y"].element_size(), B, d.n_classes,
@@ -166,11 +186,9 @@ class FusedTrainer:
         n_terms = FM._TERMS[FM.get_head_precision()]
         if n_terms and lib.fastb200_head_tc_supported(d):
             # evaluation needs no saved activations: tensor-core head (same dispatch as FAST.forward_head under no_grad)
-            key = ("packed_tc", n_terms)
-            if key not in self._ws:
-                self._ws[key] = torch.empty(lib.fastb200_head_packed_tc_bytes(d, n_terms), device=self.device, dtype=torch.uint8)
-            N.check(lib.fastb200_head_pack_tc(d, p(self.flat), p(self._ws[key]), n_terms, st), "head_pack_tc")
-            N.check(lib.fastb200_head_fwd_tc(d, p(self._ws[key]), p(ws["x"]), B, T, n_win, d.slide_step, p(ws["feat"]),
+            pk = self._packed_tc(n_terms)
+            N.check(lib.fastb200_head_pack_tc(d, p(self.flat), p(pk), n_terms, st), "head_pack_tc")
+            N.check(lib.fastb200_head_fwd_tc(d, p(pk), p(ws["x"]), B, T, n_win, d.slide_step, p(ws["feat"]),
                                              n_terms, st), "head_fwd_tc")
         else:
             N.check(lib.fastb200_head_pack(d, p(self.flat), p(self.packed), st), "head_pack")

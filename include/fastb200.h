@@ -132,6 +132,14 @@ int fastb200_head_pack_tc(const fastb200_model* m, const float* params, void* pa
 int fastb200_head_fwd_tc(const fastb200_model* m, const void* packed, const float* x, int B, int T, int n_win,
                          int step, float* feat, int n_terms, void* stream);
 
+/*
+ * Training form of fastb200_head_fwd_tc: additionally writes the activations the backward needs (y2, y3, y4 per item, fp32,
+ * the layout and size of fastb200_head_fwd's `saved`: fastb200_head_saved_floats) straight from the TMEM epilogues.
+ * Only samples t < window_len - 4 of each [F][roundup4(W-4)] row are written; the backward kernels read nothing else.
+ */
+int fastb200_head_fwd_tc_train(const fastb200_model* m, const void* packed, const float* x, int B, int T, int n_win,
+                               int step, float* feat, float* saved, int n_terms, void* stream);
+
 /* ---- zone embedding head backward with the cnn3 / cnn4 weight gradients on the tensor cores ------------------- */
 /*
  * Same function and arguments as fastb200_head_bwd (autograd of fast.py:111-119, 210, 247-251), split in two launches:

