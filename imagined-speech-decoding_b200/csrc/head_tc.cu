@@ -611,6 +611,6 @@ extern "C" int fastb200_head_fwd_tc(const fastb200_model* m, const void* packed,
 
 extern "C" int fastb200_head_fwd_tc_train(const fastb200_model* m, const void* packed, const float* x, int B, int T, int n_win,
                                           int step, float* feat, float* saved, int n_terms, void* stream) {
-    FB_REQUIRE(saved != nullptr, "head_fwd_tc_train needs the activation workspace (fastb200_head_saved_floats)");
+    FB_REQUIRE(saved != nullptr || B == 0, "head_fwd_tc_train needs the activation workspace (fastb200_head_saved_floats)");
     return head_fwd_tc_launch(m, packed, x, B, T, n_win, step, feat, saved, n_terms, stream);
 }

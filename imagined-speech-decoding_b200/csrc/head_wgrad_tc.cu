@@ -210,8 +210,8 @@ extern "C" int fastb200_head_bwd_tc(const fastb200_model* m, const float* packed
                                     const float* dfeat, int B, int T, int n_win, int step, float* gpacked, float* dx,
                                     float* work, void* stream) {
     if (int r = wgrad_tc_supported(m)) return r;
-    FB_REQUIRE(work != nullptr, "head_bwd_tc needs its workspace (fastb200_head_bwd_tc_work_floats)");
     if (B == 0) return 0;
+    FB_REQUIRE(work != nullptr, "head_bwd_tc needs its workspace (fastb200_head_bwd_tc_work_floats)");
     // input gradients of cnn4 / cnn3, the collapsed-embed weight / bias gradients and the optional dx: CUDA-core kernel
     if (int r = head_dgrad_launch(m, packed, x, saved, dfeat, B, T, n_win, step, gpacked, dx, work, stream)) return r;
     wg::Args a;

