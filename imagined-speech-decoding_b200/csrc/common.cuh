@@ -54,9 +54,10 @@ __host__ __device__ inline PackedZone packed_zone(const fastb200_model& m, int z
 }
 
 // CUDA-core part of the tensor-core-split head backward (head.cu): input gradients of cnn4 / cnn3, collapsed-embed weight
-// and bias gradients, optional dx; dL/dy4 and dL/dy3 are WRITTEN to dys (per item 2 x [F][TS]) for head_wgrad_tc.cu.
+// and bias gradients, optional dx; dL/dy4, dL/dy3 (and dL/dy2) are WRITTEN to dys (per item 3 x [F][TS]) for head_wgrad_tc.cu.
+// embed_tc != 0: the collapsed-embed weight / bias gradients are left to that kernel too (needs dx == nullptr).
 int head_dgrad_launch(const fastb200_model* m, const float* packed, const float* x, const float* saved, const float* dfeat,
-                      int B, int T, int n_win, int step, float* gpacked, float* dx, float* dys, void* stream);
+                      int B, int T, int n_win, int step, float* gpacked, float* dx, float* dys, int embed_tc, void* stream);
 
 // ---- device helpers -------------------------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {

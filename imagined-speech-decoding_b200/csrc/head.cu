@@ -50,13 +50,13 @@ __global__ void head_pack_kernel(fastb200_model m, const float* __restrict__ par
     const float* w2 = params + m.off_cnn2_w[z];
     const float* w3 = params + m.off_cnn3_w[z];
     const float* w4 = params + m.off_cnn4_w[z];
-    for (int i = threadIdx.x; i < Cz * TAPS * F; i += blockDim.x) {
+    for (int i = threadIdx.x + blockDim.x * blockIdx.y; i < Cz * TAPS * F; i += blockDim.x * gridDim.y) {
         const int f = i % F, k = (i / F) % TAPS, c = i / (F * TAPS);
         float s = 0.f;
         for (int g = 0; g < F; ++g) s = fmaf(w2[(f * F + g) * Cz + c], w1[g * TAPS + k], s);
         packed[p.weff + i] = s;
     }
-    for (int f = threadIdx.x; f < F; f += blockDim.x) {
+    for (int f = threadIdx.x + blockDim.x * blockIdx.y; f < F; f += blockDim.x * gridDim.y) {
         float s = 0.f;
         for (int g = 0; g < F; ++g) {
             float r = 0.f;
@@ -65,7 +65,7 @@ __global__ void head_pack_kernel(fastb200_model m, const float* __restrict__ par
         }
         packed[p.beff + f] = s;
     }
-    for (int i = threadIdx.x; i < F * TAPS * F; i += blockDim.x) {
+    for (int i = threadIdx.x + blockDim.x * blockIdx.y; i < F * TAPS * F; i += blockDim.x * gridDim.y) {
         const int inner = i % F, k = (i / F) % TAPS, outer = i / (F * TAPS);
         // forward layout [ci][k][co]
         packed[p.w3 + i] = w3[(inner * F + outer) * TAPS + k];
@@ -88,7 +88,7 @@ __global__ void head_unpack_grad_kernel(fastb200_model m, const float* __restric
     const float* gweff = gp + p.weff;   // [c][k][f]
     const float* gbeff = gp + p.beff;   // [f]
     // d cnn1.weight[g,k] = sum_{f,c} gweff[c,k,f] * w2[f,g,c]
-    for (int i = threadIdx.x; i < F * TAPS; i += blockDim.x) {
+    for (int i = threadIdx.x + blockDim.x * blockIdx.y; i < F * TAPS; i += blockDim.x * gridDim.y) {
         const int g = i / TAPS, k = i % TAPS;
         float s = 0.f;
         for (int f = 0; f < F; ++f)
@@ -96,7 +96,7 @@ __global__ void head_unpack_grad_kernel(fastb200_model m, const float* __restric
         grads[m.off_cnn1_w[z] + i] = s;
     }
     // d cnn1.bias[g] = sum_{f,c} gbeff[f] * w2[f,g,c]
-    for (int g = threadIdx.x; g < F; g += blockDim.x) {
+    for (int g = threadIdx.x + blockDim.x * blockIdx.y; g < F; g += blockDim.x * gridDim.y) {
         float s = 0.f;
         for (int f = 0; f < F; ++f) {
             float r = 0.f;
@@ -106,14 +106,14 @@ __global__ void head_unpack_grad_kernel(fastb200_model m, const float* __restric
         grads[m.off_cnn1_b[z] + g] = s;
     }
     // d cnn2.weight[f,g,c] = sum_k gweff[c,k,f] * w1[g,k] + gbeff[f] * b1[g]
-    for (int i = threadIdx.x; i < F * F * Cz; i += blockDim.x) {
+    for (int i = threadIdx.x + blockDim.x * blockIdx.y; i < F * F * Cz; i += blockDim.x * gridDim.y) {
         const int c = i % Cz, g = (i / Cz) % F, f = i / (Cz * F);
         float s = gbeff[f] * b1[g];
         for (int k = 0; k < TAPS; ++k) s = fmaf(gweff[(c * TAPS + k) * F + f], w1[g * TAPS + k], s);
         grads[m.off_cnn2_w[z] + i] = s;
     }
     // cnn3 / cnn4: packed [ci][k][co] -> (co, ci, 1, k)
-    for (int i = threadIdx.x; i < F * F * TAPS; i += blockDim.x) {
+    for (int i = threadIdx.x + blockDim.x * blockIdx.y; i < F * F * TAPS; i += blockDim.x * gridDim.y) {
         const int k = i % TAPS, ci = (i / TAPS) % F, co = i / (TAPS * F);
         grads[m.off_cnn3_w[z] + i] = gp[p.w3 + (ci * TAPS + k) * F + co];
         grads[m.off_cnn4_w[z] + i] = gp[p.w4 + (ci * TAPS + k) * F + co];
@@ -493,6 +493,7 @@ struct HeadDgradArgs {
     float* gpacked;
     float* dx;
     float* dys;
+    int embed_tc;       // 1: dL/dy2 is written to dys[2] and the collapsed-embed gradients are left to head_wgrad_tc.cu
     int B, T, n_win, step;
     int RS, TS, T_out, n_tt;
     int items_per_cta, n_items;
@@ -563,7 +564,7 @@ __global__ void __launch_bounds__(HEAD_THREADS, 1) head_dgrad_kernel(const __gri
         const int Cz = a.g.cz[z];
         const size_t item = (size_t)bn * a.g.Z + z;
         if (z != cur_z) {
-            if (cur_z >= 0) flush(cur_z);
+            if (cur_z >= 0 && !a.embed_tc) flush(cur_z);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 accb[i] = 0.f;
@@ -584,7 +585,7 @@ __global__ void __launch_bounds__(HEAD_THREADS, 1) head_dgrad_kernel(const __gri
             cur_z = z;
         }
         // electrodes of this window -> B (column 2 + t'), asynchronously; awaited before Q5
-        {
+        if (!a.embed_tc) {
             const int* chan = a.g.chan + a.g.zoff[z];
             const float* xb = a.x + (size_t)b * a.g.C * a.T + (size_t)n * a.step;
             const uint32_t dst0 = smem_u32(bufB);
@@ -596,7 +597,7 @@ __global__ void __launch_bounds__(HEAD_THREADS, 1) head_dgrad_kernel(const __gri
             }
             asm volatile("cp.async.commit_group;" ::: "memory");
         }
-        float* dy = a.dys + item * 2 * item_sz;
+        float* dy = a.dys + item * 3 * item_sz;
         if (tid < F) dfs[tid] = __ldg(a.dfeat + item * F + tid) * inv_T;
         mbar_wait(&bar[1], parity_y);
         parity_y ^= 1;
@@ -627,7 +628,8 @@ __global__ void __launch_bounds__(HEAD_THREADS, 1) head_dgrad_kernel(const __gri
         conv_phase<F, EPI_STORE>(bufA, F, w4t, nullptr, bufC, dy + item_sz, nullptr, RS, TS, T_out, a.n_tt);
         __syncthreads();
         // Q3: A <- dL/dy2 = conv(dy3, flipped cnn3^T)
-        conv_phase<F, EPI_STORE>(bufC, F, w3t, nullptr, bufA, nullptr, nullptr, RS, TS, T_out, a.n_tt);
+        conv_phase<F, EPI_STORE>(bufC, F, w3t, nullptr, bufA, a.embed_tc ? dy + 2 * item_sz : nullptr, nullptr, RS, TS, T_out, a.n_tt);
+        if (a.embed_tc) { __syncthreads(); continue; }
         asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncthreads();
         // Q5: dWeff += dy2 (x) x ; dbeff += sum_t dy2 ; optional dx
@@ -661,7 +663,7 @@ __global__ void __launch_bounds__(HEAD_THREADS, 1) head_dgrad_kernel(const __gri
         }
         __syncthreads();
     }
-    flush(cur_z);
+    if (!a.embed_tc) flush(cur_z);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -725,14 +727,14 @@ extern "C" int64_t fastb200_head_saved_floats(const fastb200_model* m, int B, in
 
 extern "C" int fastb200_head_pack(const fastb200_model* m, const float* params, float* packed, void* stream) {
     if (int r = validate_model(m)) return r;
-    head_pack_kernel<<<m->n_zones, 256, 0, as_stream(stream)>>>(*m, params, packed);
+    head_pack_kernel<<<dim3(m->n_zones, 8), 256, 0, as_stream(stream)>>>(*m, params, packed);
     return check_launch("head_pack");
 }
 
 extern "C" int fastb200_head_unpack_grad(const fastb200_model* m, const float* params, const float* gpacked,
                                          float* grads, void* stream) {
     if (int r = validate_model(m)) return r;
-    head_unpack_grad_kernel<<<m->n_zones, 256, 0, as_stream(stream)>>>(*m, params, gpacked, grads);
+    head_unpack_grad_kernel<<<dim3(m->n_zones, 8), 256, 0, as_stream(stream)>>>(*m, params, gpacked, grads);
     return check_launch("head_unpack_grad");
 }
 
@@ -803,7 +805,7 @@ extern "C" int fastb200_head_bwd(const fastb200_model* m, const float* packed, c
 
 int fb::head_dgrad_launch(const fastb200_model* m, const float* packed, const float* x, const float* saved,
                           const float* dfeat, int B, int T, int n_win, int step, float* gpacked, float* dx, float* dys,
-                          void* stream) {
+                          int embed_tc, void* stream) {
     if (int r = validate_model(m)) return r;
     FB_REQUIRE(B >= 0 && n_win >= 1 && step >= 1, "bad B/n_win/step");
     FB_REQUIRE(saved != nullptr && dys != nullptr, "head_dgrad needs the saved activations and the dys workspace");
@@ -812,6 +814,7 @@ int fb::head_dgrad_launch(const fastb200_model* m, const float* packed, const fl
     HeadDgradArgs a;
     a.g = make_geom(*m);
     a.packed = packed; a.x = x; a.saved = saved; a.dfeat = dfeat; a.gpacked = gpacked; a.dx = dx; a.dys = dys;
+    a.embed_tc = (embed_tc && dx == nullptr) ? 1 : 0;
     a.B = B; a.T = T; a.n_win = n_win; a.step = step;
     a.TS = head_saved_stride(W); a.T_out = head_t_out(W); a.n_tt = head_n_tt(W);
     a.RS = a.n_tt * 128 + 36;

@@ -77,7 +77,7 @@ __global__ void head_pack_tc_kernel(fastb200_model m, const float* __restrict__ 
     const float* w3 = params + m.off_cnn3_w[z];
     const float* w4 = params + m.off_cnn4_w[z];
     // collapsed cnn1 o cnn2 (same summation order as head_pack_kernel in head.cu)
-    for (int i = threadIdx.x; i < EMB_CHUNKS * 8 * F; i += blockDim.x) {
+    for (int i = threadIdx.x + blockDim.x * blockIdx.y; i < EMB_CHUNKS * 8 * F; i += blockDim.x * gridDim.y) {
         const int f = i % F, kk = i / F;
         const int k = kk / Czp, c = kk % Czp;
         float s = 0.f;
@@ -85,7 +85,7 @@ __global__ void head_pack_tc_kernel(fastb200_model m, const float* __restrict__ 
             for (int g = 0; g < F; ++g) s = fmaf(w2[(f * F + g) * Cz + c], w1[g * TAPS + k], s);
         store_split(emb, NT, kk / 8, f, kk % 8, s);
     }
-    for (int f = threadIdx.x; f < F; f += blockDim.x) {
+    for (int f = threadIdx.x + blockDim.x * blockIdx.y; f < F; f += blockDim.x * gridDim.y) {
         float s = 0.f;
         for (int g = 0; g < F; ++g) {
             float r = 0.f;
@@ -94,7 +94,7 @@ __global__ void head_pack_tc_kernel(fastb200_model m, const float* __restrict__ 
         }
         beff[f] = s;
     }
-    for (int i = threadIdx.x; i < CONV_CHUNKS * 8 * F; i += blockDim.x) {
+    for (int i = threadIdx.x + blockDim.x * blockIdx.y; i < CONV_CHUNKS * 8 * F; i += blockDim.x * gridDim.y) {
         const int co = i % F, kk = i / F;
         const int k = kk / F, ci = kk % F;
         store_split(c3, NT, kk / 8, co, kk % 8, w3[(co * F + ci) * TAPS + k]);
@@ -535,7 +535,7 @@ extern "C" int64_t fastb200_head_packed_tc_bytes(const fastb200_model* m, int n_
 
 extern "C" int fastb200_head_pack_tc(const fastb200_model* m, const float* params, void* packed, int n_terms, void* stream) {
     if (int r = tc_supported(m, n_terms)) return r;
-    tc::head_pack_tc_kernel<<<m->n_zones, 256, 0, as_stream(stream)>>>(*m, params, static_cast<uint8_t*>(packed), n_terms);
+    tc::head_pack_tc_kernel<<<dim3(m->n_zones, 8), 256, 0, as_stream(stream)>>>(*m, params, static_cast<uint8_t*>(packed), n_terms);
     return check_launch("head_pack_tc");
 }
 

@@ -54,17 +54,22 @@ __device__ __forceinline__ void umma_mn(uint32_t d_tmem, uint32_t a_lo, uint32_t
 
 struct Args {
     const float* saved;                        // per item 3 x [F][TS]: y2, y3, y4 (head_fwd)
-    const float* dys;                          // per item 2 x [F][TS]: dL/dy4, dL/dy3 (head_bwd_kernel)
+    const float* dys;                          // per item 3 x [F][TS]: dL/dy4, dL/dy3, dL/dy2 (head_dgrad_kernel)
+    const float* x;                            // (B, C, T) trials: A operand of the collapsed-embed layer (layer 2)
     float* gpacked;
     int BN, Z, TS, T_out, ksteps;
+    int n_win, step, C, T, W;
+    int cz[FASTB200_MAX_ZONES], zoff[FASTB200_MAX_ZONES], boff[FASTB200_MAX_ZONES];   // zone size / offset into chan / packed beff offset
+    int chan[FASTB200_MAX_CHANS];
     uint32_t desc_hi, lbo16;                   // descriptor high word / LBO in 16-byte units (debug: FASTB200_WG_SWAP swaps LBO and SBO)
-    int goff[FASTB200_MAX_ZONES][2];           // float offset of the packed cnn3 / cnn4 gradient block of zone z
+    int goff[FASTB200_MAX_ZONES][3];           // float offset of the packed cnn3 / cnn4 / collapsed-embed gradient block of zone z
     uint8_t cta_zone[NUM_SMS], cta_layer[NUM_SMS], cta_rank[NUM_SMS], cta_n[NUM_SMS];
 };
 
 struct Smem {
     uint64_t stg_full[2], stg_empty[2], tile_full[2], tile_empty[2], done;
     uint32_t tmem_base;
+    float bsum[F];                             // layer 2: sum_t dL/dy2 over the CTA's items (gradient of the collapsed bias)
 };
 
 __global__ void __launch_bounds__(THREADS, 1) head_wgrad_tc_kernel(const __grid_constant__ Args a) {
@@ -73,10 +78,15 @@ __global__ void __launch_bounds__(THREADS, 1) head_wgrad_tc_kernel(const __grid_
     uint8_t* tiles = smem_raw + HDR;                                // [buf][A | B]
     uint8_t* stg = tiles + 4 * TILE;                                // [2 slots][F][TS] fp32
     const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
-    const int z = a.cta_zone[blockIdx.x], layer = a.cta_layer[blockIdx.x];        // layer 0: cnn3 (A = y2, B = dy3); 1: cnn4 (y3, dy4)
+    // layer 0: cnn3 (A = y2, B = dy3); 1: cnn4 (A = y3, B = dy4); 2: collapsed cnn1 o cnn2 (A = the zone's electrodes, B = dy2)
+    const int z = a.cta_zone[blockIdx.x], layer = a.cta_layer[blockIdx.x];
+    const bool emb = layer == 2;
+    const int Cz = a.cz[z];
+    const int TSX = a.TS + 4;                                       // staging row stride of the electrode rows (W = T_out + 4 samples)
     const int rank = a.cta_rank[blockIdx.x], nc = a.cta_n[blockIdx.x];
     const int n_it = rank < a.BN ? (a.BN - rank + nc - 1) / nc : 0;
     const uint32_t tensor_bytes = (uint32_t)(F * a.TS * 4);
+    const uint32_t slot_bytes = (uint32_t)(2 * 16 * (a.TS + 4) * 4);   // staging slot: one [F][TS] tensor, or two [16][TS + 4] electrode tiles
 
     if (tid == 0) {
         for (int i = 0; i < 2; ++i) {
@@ -89,6 +99,10 @@ __global__ void __launch_bounds__(THREADS, 1) head_wgrad_tc_kernel(const __grid_
         fence_mbar_init();
     }
     for (int i = tid; i < 4 * TILE / 16; i += THREADS) reinterpret_cast<uint4*>(tiles)[i] = make_uint4(0, 0, 0, 0);
+    if (emb) {                                                      // electrode rows >= Cz of staging slot 0 stay zero
+        for (int i = tid; i < 2 * 16 * TSX; i += THREADS) reinterpret_cast<float*>(stg)[i] = 0.f;
+        if (tid < F) sm.bsum[tid] = 0.f;
+    }
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)), "n"(TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -103,15 +117,16 @@ __global__ void __launch_bounds__(THREADS, 1) head_wgrad_tc_kernel(const __grid_
     if (n_it > 0) {
         if (warp == 0) {
             // ---------------- producer: tensor loads A(0), B(0), A(1), B(1), ... into the 2-slot staging ring
+            // (embed layer: only B = dy2 -- the electrode rows are gathered by the converter warps themselves)
             if (lane == 0) {
-                for (int L = 0; L < 2 * n_it; ++L) {
+                for (int L = emb ? 1 : 0; L < 2 * n_it; L += emb ? 2 : 1) {
                     const int slot = L & 1, it = L >> 1;
                     if (L >= 2) mbar_wait(&sm.stg_empty[slot], ((L >> 1) - 1) & 1);
                     const size_t item = (size_t)(rank + it * nc) * a.Z + z;
-                    const float* src = (L & 1) == 0 ? a.saved + item * 3 * item_sz + (size_t)layer * item_sz        // y2 / y3
-                                                    : a.dys + item * 2 * item_sz + (size_t)(1 - layer) * item_sz;   // dy3 / dy4
+                    const float* src = slot == 0 ? a.saved + item * 3 * item_sz + (size_t)layer * item_sz              // y2 / y3
+                                                 : a.dys + item * 3 * item_sz + (size_t)(emb ? 2 : 1 - layer) * item_sz;   // dy3 / dy4 / dy2
                     mbar_expect_tx(&sm.stg_full[slot], tensor_bytes);
-                    bulk_g2s(stg + (size_t)slot * tensor_bytes, src, tensor_bytes, &sm.stg_full[slot]);
+                    bulk_g2s(stg + (size_t)slot * slot_bytes, src, tensor_bytes, &sm.stg_full[slot]);
                 }
             }
             __syncwarp();
@@ -136,32 +151,91 @@ __global__ void __launch_bounds__(THREADS, 1) head_wgrad_tc_kernel(const __grid_
         } else {
             // ---------------- converters: staged fp32 [c][t] -> split-bf16 tile [term][c/8][row][8]
             const int ct = tid - 64;                                 // 0 .. 255
+            float bs[4][8];
+#pragma unroll
+            for (int p = 0; p < 4; ++p)
+#pragma unroll
+                for (int e = 0; e < 8; ++e) bs[p][e] = 0.f;
+#pragma unroll 1
+            // embed layer: fused unfold + zone gather of item `it` into electrode tile it & 1 of staging slot 0, by 4-byte
+            // cp.async (trial rows are only 4-byte aligned) spread over the 256 converter threads, one item ahead
+            auto gather = [&](int it) {
+                const int bn = rank + it * nc;
+                const int b = bn / a.n_win, n = bn - b * a.n_win;
+                const float* xb = a.x + (size_t)b * a.C * a.T + (size_t)n * a.step;
+                const int* chan = a.chan + a.zoff[z];
+                const uint32_t dst0 = smem_u32(stg) + (uint32_t)(it & 1) * 16u * TSX * 4u;
+                for (int i = ct; i < Cz * a.W; i += CONV_WARPS * 32) {
+                    const int c = i / a.W, t = i - c * a.W;
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst0 + 4u * (c * TSX + t)), "l"(xb + (size_t)chan[c] * a.T + t) : "memory");
+                }
+                asm volatile("cp.async.commit_group;" ::: "memory");
+            };
+            if (emb) gather(0);
 #pragma unroll 1
             for (int it = 0; it < n_it; ++it) {
                 const int buf = it & 1;
+                if (emb) {
+                    asm volatile("cp.async.wait_group 0;" ::: "memory");                      // this thread's part of gather(it) landed
+                    asm volatile("bar.sync 1, %0;" ::"n"(CONV_WARPS * 32) : "memory");        // ... and everybody's; all are done with item it - 1
+                    if (it + 1 < n_it) gather(it + 1);                                        // tile (it + 1) & 1 was last read for item it - 1
+                }
                 if (it >= 2) mbar_wait(&sm.tile_empty[buf], ((it >> 1) - 1) & 1);
 #pragma unroll 1
                 for (int half = 0; half < 2; ++half) {
                     const int L = 2 * it + half, slot = L & 1;
-                    mbar_wait(&sm.stg_full[slot], (L >> 1) & 1);
-                    const float* sg = reinterpret_cast<const float*>(stg + (size_t)slot * tensor_bytes);
-                    uint8_t* tile = tiles + buf * 2 * TILE + half * TILE + (half == 0 ? 2 * 16 : 0);     // A rows are shifted by the 2 pad rows
-                    for (int t = ct; t < a.T_out; t += CONV_WARPS * 32) {
+                    if (!(emb && half == 0)) mbar_wait(&sm.stg_full[slot], (L >> 1) & 1);
+                    const float* sg = (emb && half == 0) ? reinterpret_cast<const float*>(stg) + (it & 1) * 16 * TSX
+                                                         : reinterpret_cast<const float*>(stg + (size_t)slot * slot_bytes);
+                    if (emb && half == 0) {
+                        // electrodes: 16 channels (2 planes per term: a0 -> M rows 0-15, a1 -> 16-31), rows = samples 0 .. W-1
+                        uint8_t* tile = tiles + buf * 2 * TILE;
+                        for (int t = ct; t < a.W; t += CONV_WARPS * 32) {
 #pragma unroll
-                        for (int p = 0; p < 4; ++p) {
-                            float v[8];
+                            for (int p = 0; p < 2; ++p) {
+                                float v[8];
 #pragma unroll
-                            for (int e = 0; e < 8; ++e) v[e] = sg[(8 * p + e) * a.TS + t];
-                            uint4 o[2];
-                            split8<2>(v, o);
-                            *reinterpret_cast<uint4*>(tile + p * PLANE + t * 16) = o[0];
-                            *reinterpret_cast<uint4*>(tile + (4 + p) * PLANE + t * 16) = o[1];
+                                for (int e = 0; e < 8; ++e) v[e] = sg[(8 * p + e) * TSX + t];
+                                uint4 o[2];
+                                split8<2>(v, o);
+                                *reinterpret_cast<uint4*>(tile + p * PLANE + t * 16) = o[0];
+                                *reinterpret_cast<uint4*>(tile + (2 + p) * PLANE + t * 16) = o[1];
+                            }
+                        }
+                    } else {
+                        uint8_t* tile = tiles + buf * 2 * TILE + half * TILE + (half == 0 ? 2 * 16 : 0);     // A rows are shifted by the 2 pad rows
+                        for (int t = ct; t < a.T_out; t += CONV_WARPS * 32) {
+#pragma unroll
+                            for (int p = 0; p < 4; ++p) {
+                                float v[8];
+#pragma unroll
+                                for (int e = 0; e < 8; ++e) v[e] = sg[(8 * p + e) * a.TS + t];
+                                if (emb) {
+#pragma unroll
+                                    for (int e = 0; e < 8; ++e) bs[p][e] += v[e];
+                                }
+                                uint4 o[2];
+                                split8<2>(v, o);
+                                *reinterpret_cast<uint4*>(tile + p * PLANE + t * 16) = o[0];
+                                *reinterpret_cast<uint4*>(tile + (4 + p) * PLANE + t * 16) = o[1];
+                            }
                         }
                     }
                     fence_proxy_async();
-                    mbar_arrive(&sm.stg_empty[slot]);
+                    if (!(emb && half == 0)) mbar_arrive(&sm.stg_empty[slot]);
                     mbar_arrive(&sm.tile_full[buf]);
                 }
+            }
+            if (emb) {
+#pragma unroll
+                for (int p = 0; p < 4; ++p)
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        const float r = warp_sum(bs[p][e]);
+                        if (lane == 0) atomicAdd(&sm.bsum[8 * p + e], r);
+                    }
+                asm volatile("bar.sync 1, %0;" ::"n"(CONV_WARPS * 32) : "memory");
+                if (ct < F) atomicAdd(a.gpacked + a.boff[z] + ct, sm.bsum[ct]);
             }
         }
         // ---------------- drain: lanes 0-31 hold the a0 rows, 32-63 the a1 rows; columns [b0 | b1] per tap
@@ -169,14 +243,20 @@ __global__ void __launch_bounds__(THREADS, 1) head_wgrad_tc_kernel(const __grid_
             mbar_wait(&sm.done, 0);
             tc_fence_after();
             float* g = a.gpacked + a.goff[z][layer];
+            if (!emb || warp == 0) {
+                const int row = emb ? (lane & 15) : lane;           // embed: lanes 0-15 = a0 rows, 16-31 = a1 rows (channel = lane & 15)
+                const bool ok = !emb || row < Cz;
 #pragma unroll 1
-            for (int k = 0; k < TAPS; ++k) {
-                float v0[32], v1[32];
-                const uint32_t addr = tmem + ((uint32_t)(32 * warp) << 16) + k * NCOL;
-                tmem_ld32(addr, v0);
-                tmem_ld32(addr + 32, v1);
+                for (int k = 0; k < TAPS; ++k) {
+                    float v0[32], v1[32];
+                    const uint32_t addr = tmem + ((uint32_t)(32 * warp) << 16) + k * NCOL;
+                    tmem_ld32(addr, v0);
+                    tmem_ld32(addr + 32, v1);
+                    if (ok) {
 #pragma unroll
-                for (int co = 0; co < 32; ++co) atomicAdd(g + (lane * TAPS + k) * F + co, v0[co] + v1[co]);
+                        for (int co = 0; co < 32; ++co) atomicAdd(g + (row * TAPS + k) * F + co, v0[co] + v1[co]);
+                    }
+                }
             }
         }
     }
@@ -203,7 +283,7 @@ extern "C" int fastb200_head_bwd_tc_supported(const fastb200_model* m) { return 
 
 extern "C" int64_t fastb200_head_bwd_tc_work_floats(const fastb200_model* m, int B, int n_win) {
     if (wgrad_tc_supported(m)) return -1;
-    return (int64_t)B * n_win * m->n_zones * 2 * m->dim_cnn * head_saved_stride(m->window_len);
+    return (int64_t)B * n_win * m->n_zones * 3 * m->dim_cnn * head_saved_stride(m->window_len);
 }
 
 extern "C" int fastb200_head_bwd_tc(const fastb200_model* m, const float* packed, const float* x, const float* saved,
@@ -212,30 +292,36 @@ extern "C" int fastb200_head_bwd_tc(const fastb200_model* m, const float* packed
     if (int r = wgrad_tc_supported(m)) return r;
     if (B == 0) return 0;
     FB_REQUIRE(work != nullptr, "head_bwd_tc needs its workspace (fastb200_head_bwd_tc_work_floats)");
-    // input gradients of cnn4 / cnn3, the collapsed-embed weight / bias gradients and the optional dx: CUDA-core kernel
-    if (int r = head_dgrad_launch(m, packed, x, saved, dfeat, B, T, n_win, step, gpacked, dx, work, stream)) return r;
+    // the collapsed-embed weight / bias gradients join the tensor-core kernel when no input gradient is wanted (training) and
+    // every zone fits the 16-channel electrode tile; otherwise the CUDA-core kernel keeps them (and dx)
+    bool embed_tc = dx == nullptr;
+    for (int z = 0; z < m->n_zones; ++z) embed_tc = embed_tc && m->zone_size[z] <= 16;
+    if (int r = head_dgrad_launch(m, packed, x, saved, dfeat, B, T, n_win, step, gpacked, dx, work, embed_tc ? 1 : 0, stream)) return r;
     wg::Args a;
-    a.saved = saved; a.dys = work; a.gpacked = gpacked;
+    a.saved = saved; a.dys = work; a.gpacked = gpacked; a.x = x;
     a.BN = B * n_win; a.Z = m->n_zones; a.TS = head_saved_stride(m->window_len); a.T_out = m->window_len - 4;
     a.ksteps = ceil_div(a.T_out, 16);
+    a.n_win = n_win; a.step = step; a.C = m->n_chan; a.T = T; a.W = m->window_len;
     a.desc_hi = wg::DESC_HI_MN; a.lbo16 = 128u >> 4;
     if (const char* sw = getenv("FASTB200_WG_SWAP")) if (atoi(sw)) { a.desc_hi = (128u >> 4) | (1u << 14); a.lbo16 = (uint32_t)(wg::PLANE >> 4); }
-    const int F = m->dim_cnn;
+    int n_sel = 0;
     for (int z = 0; z < m->n_zones; ++z) {
         const PackedZone p = packed_zone(*m, z);
-        a.goff[z][0] = p.w3; a.goff[z][1] = p.w4;
+        a.goff[z][0] = p.w3; a.goff[z][1] = p.w4; a.goff[z][2] = p.weff; a.boff[z] = p.beff;
+        a.cz[z] = m->zone_size[z]; a.zoff[z] = m->zone_off[z]; n_sel += m->zone_size[z];
     }
-    (void)F;
-    const int pairs = 2 * m->n_zones;
-    const int grid = NUM_SMS >= pairs ? NUM_SMS : pairs;
+    for (int i = 0; i < n_sel; ++i) a.chan[i] = m->zone_chan[i];
+    const int layers = embed_tc ? 3 : 2;
+    const int groups = layers * m->n_zones;                  // one (zone, layer) group per CTA; equal cost per item
+    const int grid = NUM_SMS >= groups ? NUM_SMS : groups;
     int c = 0;
-    for (int p = 0; p < pairs; ++p) {
-        const int n = grid / pairs + (p < grid % pairs ? 1 : 0);
+    for (int p = 0; p < groups; ++p) {
+        const int n = grid / groups + (p < grid % groups ? 1 : 0);
         for (int r = 0; r < n; ++r, ++c) {
-            a.cta_zone[c] = (uint8_t)(p >> 1); a.cta_layer[c] = (uint8_t)(p & 1); a.cta_rank[c] = (uint8_t)r; a.cta_n[c] = (uint8_t)n;
+            a.cta_zone[c] = (uint8_t)(p / layers); a.cta_layer[c] = (uint8_t)(p % layers); a.cta_rank[c] = (uint8_t)r; a.cta_n[c] = (uint8_t)n;
         }
     }
-    const size_t smem = wg::HDR + 4 * wg::TILE + 2 * (size_t)wg::F * a.TS * 4;
+    const size_t smem = wg::HDR + 4 * wg::TILE + 2 * (size_t)(2 * 16 * (a.TS + 4) * 4);
     cudaError_t e = cudaFuncSetAttribute(wg::head_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return fail((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     wg::head_wgrad_tc_kernel<<<grid, wg::THREADS, smem, as_stream(stream)>>>(a);

@@ -147,7 +147,9 @@ int fastb200_head_fwd_tc_train(const fastb200_model* m, const void* packed, cons
  * optional dx, and WRITES dL/dy4, dL/dy3 to `work`; a tcgen05 kernel then forms the cnn3 / cnn4 weight gradients
  * (per tap a (32 x T) x (T x 32) contraction over time, split-bf16 operands, fp32 accumulation in TMEM across all items).
  * Shapes supported: dim_cnn == 32, 20 <= window_len <= 260 (fastb200_head_bwd_tc_supported() returns 1).
- *   work: fastb200_head_bwd_tc_work_floats(m, B, n_win) floats (B*n_win*Z items x 2 x F x roundup4(W-4)).
+ * When dx == NULL (training) and every zone has <= 16 electrodes the collapsed-embed weight / bias gradients are formed by
+ * the tcgen05 kernel as well (A operand = the zone's electrodes, gathered from x by 4-byte cp.async).
+ *   work: fastb200_head_bwd_tc_work_floats(m, B, n_win) floats (B*n_win*Z items x 3 x F x roundup4(W-4): dL/dy4, dL/dy3, dL/dy2).
  */
 int     fastb200_head_bwd_tc_supported(const fastb200_model* m);
 int64_t fastb200_head_bwd_tc_work_floats(const fastb200_model* m, int B, int n_win);
