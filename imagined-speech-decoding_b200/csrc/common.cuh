@@ -59,6 +59,12 @@ __host__ __device__ inline PackedZone packed_zone(const fastb200_model& m, int z
 int head_dgrad_launch(const fastb200_model* m, const float* packed, const float* x, const float* saved, const float* dfeat,
                       int B, int T, int n_win, int step, float* gpacked, float* dx, float* dys, int embed_tc, void* stream);
 
+// Tensor-core input-gradient chain (head_dgrad_tc.cu): writes dL/dy4, dL/dy3, dL/dy2 to dys; fpacked = head_pack output.
+int head_dgrad_tc_supported(const fastb200_model* m);
+int64_t head_dgrad_tc_packed_bytes(const fastb200_model* m, int n_terms);
+int head_dgrad_tc_launch(const fastb200_model* m, const float* fpacked, const float* saved, const float* dfeat, int B,
+                         int n_win, float* dys, void* packed_ws, int n_terms, void* stream);
+
 // ---- device helpers -------------------------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

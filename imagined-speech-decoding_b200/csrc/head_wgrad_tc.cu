@@ -283,7 +283,8 @@ extern "C" int fastb200_head_bwd_tc_supported(const fastb200_model* m) { return 
 
 extern "C" int64_t fastb200_head_bwd_tc_work_floats(const fastb200_model* m, int B, int n_win) {
     if (wgrad_tc_supported(m)) return -1;
-    return (int64_t)B * n_win * m->n_zones * 3 * m->dim_cnn * head_saved_stride(m->window_len);
+    // dL/dy4, dL/dy3, dL/dy2 per item + the split-bf16 transposed cnn3 / cnn4 weights of the tensor-core input-gradient kernel
+    return (int64_t)B * n_win * m->n_zones * 3 * m->dim_cnn * head_saved_stride(m->window_len) + head_dgrad_tc_packed_bytes(m, 3) / 4;
 }
 
 extern "C" int fastb200_head_bwd_tc(const fastb200_model* m, const float* packed, const float* x, const float* saved,
@@ -296,7 +297,12 @@ extern "C" int fastb200_head_bwd_tc(const fastb200_model* m, const float* packed
     // every zone fits the 16-channel electrode tile; otherwise the CUDA-core kernel keeps them (and dx)
     bool embed_tc = dx == nullptr;
     for (int z = 0; z < m->n_zones; ++z) embed_tc = embed_tc && m->zone_size[z] <= 16;
-    if (int r = head_dgrad_launch(m, packed, x, saved, dfeat, B, T, n_win, step, gpacked, dx, work, embed_tc ? 1 : 0, stream)) return r;
+    const char* dg_env = getenv("FASTB200_DGRAD");                                    // debug: "ffma" forces the CUDA-core chain
+    const int dg_terms = (dg_env && atoi(dg_env) == 3) ? 3 : 2;
+    if (embed_tc && head_dgrad_tc_supported(m) && !(dg_env && dg_env[0] == 'f')) {
+        float* pk = work + (int64_t)B * n_win * m->n_zones * 3 * m->dim_cnn * head_saved_stride(m->window_len);
+        if (int r = head_dgrad_tc_launch(m, packed, saved, dfeat, B, n_win, work, pk, dg_terms, stream)) return r;
+    } else if (int r = head_dgrad_launch(m, packed, x, saved, dfeat, B, T, n_win, step, gpacked, dx, work, embed_tc ? 1 : 0, stream)) return r;
     wg::Args a;
     a.saved = saved; a.dys = work; a.gpacked = gpacked; a.x = x;
     a.BN = B * n_win; a.Z = m->n_zones; a.TS = head_saved_stride(m->window_len); a.T_out = m->window_len - 4;
