@@ -713,7 +713,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=8192)
     ap.add_argument("--no-extras", action="store_true")
-    ap.add_argument("--head-precision", default=os.environ.get("FASTB200_HEAD_PRECISION", "bf16x3"), choices=["bf16x3", "bf16x2", "fp32"])
+    ap.add_argument("--head-precision", default=os.environ.get("FASTB200_HEAD_PRECISION", "bf16x2"), choices=["bf16x3", "bf16x2", "fp32"])
     ap.add_argument("--e2e-chunk", type=int, default=1024, help="trials per H2D piece of the end-to-end run")
     ap.add_argument("--cpu-trials", type=int, default=4096, help="trials of the bounded CPU-baseline sample (~10 s)")
     ap.add_argument("--workload", default="infer", choices=["infer", "train", "preprocess", "cv", "stress"],

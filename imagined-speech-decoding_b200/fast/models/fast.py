@@ -27,12 +27,13 @@ from .. import _native as N
 __all__ = ["FAST", "AttentionBlock", "CVBlock", "Conv4Layers", "EEGNet_Encoder", "HeadConv_Paper_Version", "Head",
            "set_head_precision", "get_head_precision", "set_head_backward", "get_head_backward"]
 
-# Arithmetic of the Conv4Layers head when no gradient is needed (inference):
-#   'bf16x3'  tcgen05 tensor cores, every fp32 operand split into 3 bf16 terms (24 mantissa bits, fp32-equivalent)
-#   'bf16x2'  tcgen05 tensor cores, 2 bf16 terms (16 mantissa bits; features still ~1e-6: they are 246-sample means)
-#   'fp32'    CUDA-core FFMA kernel (also what every shape the tensor-core kernel does not cover falls to, and what
-#             training uses: its forward saves the activations the backward kernel needs)
-_HEAD_PRECISION = os.environ.get("FASTB200_HEAD_PRECISION", "bf16x3")
+# Arithmetic of the Conv4Layers head forward (inference and training):
+#   'bf16x2'  tcgen05 tensor cores, every fp32 operand split into 2 bf16 terms (16 mantissa bits; features ~5e-6, every
+#             gradient tensor < 1e-4 of the fp32 reference -- the default; the reference itself trains under bf16-mixed
+#             autocast, scripts/train_fast.py:277)
+#   'bf16x3'  tcgen05 tensor cores, 3 bf16 terms (24 mantissa bits, fp32-equivalent: features ~1.4e-6)
+#   'fp32'    CUDA-core FFMA kernels (also what every shape the tensor-core kernels do not cover falls to)
+_HEAD_PRECISION = os.environ.get("FASTB200_HEAD_PRECISION", "bf16x2")
 _TERMS = {"bf16x3": 3, "bf16x2": 2, "fp32": 0}
 
 

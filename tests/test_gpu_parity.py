@@ -130,10 +130,13 @@ def head_backward():
     FM.set_head_backward(old)
 
 
-@pytest.mark.parametrize("bwd", ["ffma", "tc"])
-def test_prod_backward(golden, head_backward, head_precision, bwd):
-    head_backward(bwd)                                            # 'ffma': CUDA-core forward + backward; 'tc': tensor-core training
-    head_precision("fp32" if bwd == "ffma" else "bf16x3")         # forward (saves y2..y4) + tensor-core weight gradients
+TRAIN_PATHS = [("ffma", "fp32"), ("tc", "bf16x2"), ("tc", "bf16x3")]   # (head backward, head forward arithmetic)
+
+
+@pytest.mark.parametrize("bwd,prec", TRAIN_PATHS)
+def test_prod_backward(golden, head_backward, head_precision, bwd, prec):
+    head_backward(bwd)                                            # 'ffma': CUDA-core forward + backward; 'tc': tcgen05 forward
+    head_precision(prec)                                          # (saves y2..y4), input-gradient chain and weight gradients
     m = _prod_model().eval()                                      # golden gradients were taken in eval mode
     x = _prod_x().cuda().requires_grad_(True)
     y = torch.from_numpy(golden["prod/y"]).cuda()
@@ -156,11 +159,11 @@ def test_prod_backward(golden, head_backward, head_precision, bwd):
     assert abs(dfp[3] - golden["prod/dx_fp"][3]) / golden["prod/dx_fp"][3] < 1e-3
 
 
-@pytest.mark.parametrize("bwd", ["ffma", "tc"])
-def test_prod_backward_vs_oracle_all_tensors(head_backward, head_precision, bwd):
+@pytest.mark.parametrize("bwd,prec", TRAIN_PATHS)
+def test_prod_backward_vs_oracle_all_tensors(head_backward, head_precision, bwd, prec):
     """Every one of the 94 gradient tensors against the oracle's autograd on a fresh input (not only the golden subset)."""
     head_backward(bwd)
-    head_precision("fp32" if bwd == "ffma" else "bf16x3")
+    head_precision(prec)
     m = _prod_model().eval()
     sd = {k: v.detach().cpu() for k, v in m.state_dict().items()}
     g = torch.Generator().manual_seed(77)
@@ -529,12 +532,12 @@ def test_head_bwd_tc_weight_gradients_vs_ffma_at_scale(head_backward, head_preci
     grads = {}
     for bwd in ("ffma", "tc"):
         head_backward(bwd)
-        head_precision("fp32" if bwd == "ffma" else "bf16x3")
+        head_precision("fp32" if bwd == "ffma" else "bf16x2")
         m.zero_grad(set_to_none=True)
         torch.nn.CrossEntropyLoss()(m(x), y).backward()
         grads[bwd] = {k: p.grad.clone() for k, p in m.named_parameters()}
     for k in grads["ffma"]:
         e = rel_err(grads["tc"][k], grads["ffma"][k])
         assert e < TOL, (k, e)
-    worst = max(rel_err(grads["tc"][k], grads["ffma"][k]) for k in grads["tc"] if "cnn3" in k or "cnn4" in k)
-    print("worst cnn3/cnn4 weight-gradient deviation tc vs ffma:", worst)
+    worst = max(rel_err(grads["tc"][k], grads["ffma"][k]) for k in grads["tc"])
+    assert worst < TOL / 2, worst            # measured on B200: 1.1e-5 (bf16x2 forward, 2-term input-gradient chain and weight gradients)
