@@ -596,6 +596,8 @@ def run_cv(args, rank, world, local_rank):
     if rank == 0:
         shutil.rmtree(save, ignore_errors=True)
         os.makedirs(save, exist_ok=True)
+    if dist is not None:
+        dist.barrier()                                  # nobody writes into the tree before rank 0 has cleaned it
     data = {}
 
     def load(sid):
