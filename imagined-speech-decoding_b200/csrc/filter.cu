@@ -125,6 +125,7 @@ __global__ void __launch_bounds__(FILT_WARPS * 32) sosfiltfilt_kernel(const __gr
 }
 
 // y[j] = sum_i x[i] * h[(j + n_pre_remove) * down - i * up]
+constexpr int RS_MAXT = 28;        // taps per polyphase branch held in registers (scipy's default FIR: 20 * max(up, down) + 1 taps)
 template <typename XT, typename YT>
 __global__ void __launch_bounds__(FILT_WARPS * 32) resample_poly_kernel(const XT* __restrict__ x, YT* __restrict__ y,
                                                                         int64_t rows, int T_in, int T_out,
@@ -137,11 +138,42 @@ __global__ void __launch_bounds__(FILT_WARPS * 32) resample_poly_kernel(const XT
     __syncthreads();
     if (warp >= warps_per_cta) return;
     double* xs = fsm + ((len_h + 1) & ~1) + (size_t)warp * T_in;
+    // a lane's outputs j = lane, lane + 32, ... share the filter phase r = ((j + n_pre_remove) * down) % up when up | 32 * down
+    const bool fast = (32 * down) % up == 0 && (len_h + up - 1) / up <= RS_MAXT;
+    double cf[RS_MAXT];
+    {
+        const int r = ((lane + n_pre_remove) * down) % up;
+#pragma unroll
+        for (int q = 0; q < RS_MAXT; ++q) cf[q] = (fast && r + q * up < len_h) ? hs[r + q * up] : 0.0;
+    }
     for (int64_t row = (int64_t)blockIdx.x * warps_per_cta + warp; row < rows; row += (int64_t)gridDim.x * warps_per_cta) {
         const XT* xr = x + row * T_in;
         for (int t = lane; t < T_in; t += 32) xs[t] = (double)xr[t];
         __syncwarp();
         YT* yr = y + row * T_out;
+        if (fast) {
+            // polyphase fast path: this lane's outputs all use the same sub-filter (phase r), held in registers, so a tap
+            // costs one shared-memory read instead of two (the kernel is shared-memory-bandwidth bound on fp64 operands)
+            for (int j = lane; j < T_out; j += 32) {
+                const int pos = (j + n_pre_remove) * down;
+                const int i_hi = pos / up;
+                double acc = 0.0;
+                if (i_hi <= T_in - 1) {
+#pragma unroll
+                    for (int q = RS_MAXT - 1; q >= 0; --q) {
+                        const int i = i_hi - q;
+                        if (i >= 0) acc = fma(xs[i], cf[q], acc);          // cf[q] == 0 past the end of the filter
+                    }
+                } else {                                                    // right edge: the input ran out before the filter did
+                    int i_lo = pos - len_h + 1;
+                    i_lo = i_lo <= 0 ? 0 : (i_lo + up - 1) / up;
+                    for (int i = i_lo; i <= T_in - 1; ++i) acc = fma(xs[i], hs[pos - i * up], acc);
+                }
+                yr[j] = (YT)acc;
+            }
+            __syncwarp();
+            continue;
+        }
         for (int j = lane; j < T_out; j += 32) {
             const int pos = (j + n_pre_remove) * down;
             int i_hi = pos / up;

@@ -56,14 +56,20 @@ __global__ void head_pack_kernel(fastb200_model m, const float* __restrict__ par
         for (int g = 0; g < F; ++g) s = fmaf(w2[(f * F + g) * Cz + c], w1[g * TAPS + k], s);
         packed[p.weff + i] = s;
     }
-    for (int f = threadIdx.x + blockDim.x * blockIdx.y; f < F; f += blockDim.x * gridDim.y) {
-        float s = 0.f;
-        for (int g = 0; g < F; ++g) {
-            float r = 0.f;
-            for (int c = 0; c < Cz; ++c) r += w2[(f * F + g) * Cz + c];
-            s = fmaf(r, b1[g], s);
+    // beff[f] = sum_g b1[g] * sum_c w2[f,g,c]: one warp per f, lane = g (a serial 32 x Cz chain of dependent loads per thread
+    // made this tiny kernel 40 us long)
+    {
+        const int lane = threadIdx.x & 31, wg = (threadIdx.x >> 5) + (blockDim.x >> 5) * blockIdx.y, nw = (blockDim.x >> 5) * gridDim.y;
+        for (int f = wg; f < F; f += nw) {
+            float v = 0.f;
+            if (lane < F) {
+                float r = 0.f;
+                for (int c = 0; c < Cz; ++c) r += w2[(f * F + lane) * Cz + c];
+                v = r * b1[lane];
+            }
+            v = warp_sum(v);
+            if (lane == 0) packed[p.beff + f] = v;
         }
-        packed[p.beff + f] = s;
     }
     for (int i = threadIdx.x + blockDim.x * blockIdx.y; i < F * TAPS * F; i += blockDim.x * gridDim.y) {
         const int inner = i % F, k = (i / F) % TAPS, outer = i / (F * TAPS);
@@ -88,22 +94,26 @@ __global__ void head_unpack_grad_kernel(fastb200_model m, const float* __restric
     const float* gweff = gp + p.weff;   // [c][k][f]
     const float* gbeff = gp + p.beff;   // [f]
     // d cnn1.weight[g,k] = sum_{f,c} gweff[c,k,f] * w2[f,g,c]
-    for (int i = threadIdx.x + blockDim.x * blockIdx.y; i < F * TAPS; i += blockDim.x * gridDim.y) {
+    // (one warp per output, lane = f: the serial F x Cz chains of dependent loads dominated this kernel)
+    const int lane = threadIdx.x & 31, wg = (threadIdx.x >> 5) + (blockDim.x >> 5) * blockIdx.y, nw = (blockDim.x >> 5) * gridDim.y;
+    for (int i = wg; i < F * TAPS; i += nw) {
         const int g = i / TAPS, k = i % TAPS;
         float s = 0.f;
-        for (int f = 0; f < F; ++f)
-            for (int c = 0; c < Cz; ++c) s = fmaf(gweff[(c * TAPS + k) * F + f], w2[(f * F + g) * Cz + c], s);
-        grads[m.off_cnn1_w[z] + i] = s;
+        if (lane < F)
+            for (int c = 0; c < Cz; ++c) s = fmaf(gweff[(c * TAPS + k) * F + lane], w2[(lane * F + g) * Cz + c], s);
+        s = warp_sum(s);
+        if (lane == 0) grads[m.off_cnn1_w[z] + i] = s;
     }
     // d cnn1.bias[g] = sum_{f,c} gbeff[f] * w2[f,g,c]
-    for (int g = threadIdx.x + blockDim.x * blockIdx.y; g < F; g += blockDim.x * gridDim.y) {
+    for (int g = wg; g < F; g += nw) {
         float s = 0.f;
-        for (int f = 0; f < F; ++f) {
+        if (lane < F) {
             float r = 0.f;
-            for (int c = 0; c < Cz; ++c) r += w2[(f * F + g) * Cz + c];
-            s = fmaf(gbeff[f], r, s);
+            for (int c = 0; c < Cz; ++c) r += w2[(lane * F + g) * Cz + c];
+            s = gbeff[lane] * r;
         }
-        grads[m.off_cnn1_b[z] + g] = s;
+        s = warp_sum(s);
+        if (lane == 0) grads[m.off_cnn1_b[z] + g] = s;
     }
     // d cnn2.weight[f,g,c] = sum_k gweff[c,k,f] * w1[g,k] + gbeff[f] * b1[g]
     for (int i = threadIdx.x + blockDim.x * blockIdx.y; i < F * F * Cz; i += blockDim.x * gridDim.y) {

@@ -85,14 +85,17 @@ __global__ void head_pack_tc_kernel(fastb200_model m, const float* __restrict__ 
             for (int g = 0; g < F; ++g) s = fmaf(w2[(f * F + g) * Cz + c], w1[g * TAPS + k], s);
         store_split(emb, NT, kk / 8, f, kk % 8, s);
     }
-    for (int f = threadIdx.x + blockDim.x * blockIdx.y; f < F; f += blockDim.x * gridDim.y) {
-        float s = 0.f;
-        for (int g = 0; g < F; ++g) {
+    {   // beff[f] = sum_g b1[g] * sum_c w2[f,g,c]: one warp per f, lane = g (as head_pack_kernel)
+        const int lane = threadIdx.x & 31, wg = (threadIdx.x >> 5) + (blockDim.x >> 5) * blockIdx.y, nw = (blockDim.x >> 5) * gridDim.y;
+        for (int f = wg; f < F; f += nw) {
             float r = 0.f;
-            for (int c = 0; c < Cz; ++c) r += w2[(f * F + g) * Cz + c];
-            s = fmaf(r, b1[g], s);
+            if (lane < F) {
+                for (int c = 0; c < Cz; ++c) r += w2[(f * F + lane) * Cz + c];
+                r *= b1[lane];
+            }
+            const float v = warp_sum(r);
+            if (lane == 0) beff[f] = v;
         }
-        beff[f] = s;
     }
     for (int i = threadIdx.x + blockDim.x * blockIdx.y; i < CONV_CHUNKS * 8 * F; i += blockDim.x * gridDim.y) {
         const int co = i % F, kk = i / F;

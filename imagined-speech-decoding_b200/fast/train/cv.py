@@ -6,9 +6,10 @@ jobs and there is NO data-path collective; the only join is on the host: per sub
 subject's test set" (train_fast.py:182-212) and the summary CSVs (:226-240).
 
 One job = the reference's ``trainer.fit`` for one fold, with the Lightning loop replaced by a device-resident loop:
-the subject's trials stay in HBM (72 MB), batches are index gathers on the device, every step is the CUDA-graphed
-``FusedTrainer`` step, metrics accumulate on the device and the best-``val_acc`` weights are kept by a predicated
-device copy -- the host never synchronises inside a job.  Artefacts keep the reference's names and formats
+the subject's trials stay in HBM (72 MB), batches are index gathers on the device, and a WHOLE EPOCH -- the batch
+gathers, the fused training steps, the validation pass, the metric row and the predicated best-``val_acc`` snapshot --
+is one CUDA graph replayed once per epoch (the host only draws the next permutation), so the host neither synchronises
+inside a job nor limits it when several ranks share one host.  Artefacts keep the reference's names and formats
 (``sub-XX/fold-k_history.csv``, ``fold_metrics.csv``, ``best_subject.pth``, ``test_predictions.csv``,
 ``summary_per_subject.csv``, ``global_test_predictions.csv``) so ``scripts/benchmark.py`` reads them unchanged.
 
@@ -133,34 +134,66 @@ def train_fold(config, x, y, train_idx, val_idx, max_epochs=200, batch_size=64, 
     if warmup_epochs > max_epochs:                            # the stock warmup_epochs=10 asserts for short runs
         warmup_epochs = 0
     sched = cosine_scheduler(1, 0.1, max_epochs, n_it, warmup_epochs=warmup_epochs)
-    ft = FusedTrainer(model, lr=lr, lr_factors=lightning_lr_factors(sched), use_graph=use_graph, seed=seed)
+    ft = FusedTrainer(model, lr=lr, lr_factors=lightning_lr_factors(sched), use_graph=False, seed=seed)   # the graph is per EPOCH, below
     gen = torch.Generator(device=dev).manual_seed(seed)
-    xv, yv = x[va], y[va]
+    xv, yv = x[va].contiguous(), y[va].contiguous()
+    if y.dtype not in (torch.uint8, torch.int64):
+        y, yv = y.long(), yv.long()
     hist = torch.zeros(max_epochs, 4, device=dev, dtype=torch.float64)
     best_correct = torch.full((1,), -1, device=dev, dtype=torch.int32)
     best_epoch = torch.zeros(1, device=dev, dtype=torch.int32)
     best_flat = ft.flat.clone()
     loss_sum = torch.zeros(1, device=dev, dtype=torch.float64)
     corr_sum = torch.zeros(1, device=dev, dtype=torch.int64)
-    for ep in range(max_epochs):
-        model.train()
-        perm = tr[torch.randperm(n_tr, device=dev, generator=gen)]
+    perm = torch.empty(n_tr, device=dev, dtype=torch.int64)   # this epoch's shuffled trial indices (fixed address: graph input)
+    ep_dev = torch.zeros(1, device=dev, dtype=torch.int64)    # epoch counter, advanced inside the epoch graph
+    T = x.shape[2]
+    sizes = [min(batch_size, n_tr - lo) for lo in range(0, n_tr, batch_size)]
+
+    def epoch_body():
+        """One whole epoch as stream-ordered launches only (no host reads, fixed buffers): batch gathers, the fused
+        training steps, the validation pass, the metric row and the best-epoch snapshot.  Capturable as ONE CUDA graph."""
         loss_sum.zero_(); corr_sum.zero_()
-        for lo in range(0, n_tr, batch_size):
-            idx = perm[lo:lo + batch_size]
-            loss, ncorr = ft.train_step(x[idx], y[idx])
-            loss_sum += loss.double() * idx.numel()          # Lightning's on_epoch mean is batch-size weighted
-            corr_sum += ncorr
-        model.eval()
-        vloss, vcorr, _ = ft.eval_step(xv, yv)
-        hist[ep, 0] = (loss_sum / n_tr)[0]
-        hist[ep, 1] = (corr_sum.double() / n_tr)[0]
-        hist[ep, 2] = vloss[0].double()
-        hist[ep, 3] = vcorr[0].double() / n_va
+        lo = 0
+        for b in sizes:
+            ws = ft._workspace(b, T, y.dtype, True)
+            idx = perm[lo:lo + b]
+            torch.index_select(x, 0, idx, out=ws["x"])
+            torch.index_select(y, 0, idx, out=ws["y"])
+            ft._launch_train(ws)
+            loss_sum.add_(ft.loss.double() * b)               # Lightning's on_epoch mean is batch-size weighted
+            corr_sum.add_(ft.n_correct)
+            lo += b
+        wsv = ft._workspace(n_va, T, y.dtype, False)
+        wsv["x"].copy_(xv); wsv["y"].copy_(yv)
+        ft._launch_eval(wsv)
+        vcorr = ft.n_correct
+        row = torch.cat([loss_sum / n_tr, corr_sum.double() / n_tr, ft.loss.double(), vcorr.double() / n_va]).unsqueeze(0)
+        hist.index_copy_(0, ep_dev, row)
         better = vcorr > best_correct                         # (1,) bool, stays on the device
-        best_flat = torch.where(better, ft.flat, best_flat)
-        best_epoch = torch.where(better, torch.full_like(best_epoch, ep), best_epoch)
-        best_correct = torch.maximum(best_correct, vcorr)
+        best_flat.copy_(torch.where(better, ft.flat, best_flat))
+        best_epoch.copy_(torch.where(better, ep_dev.to(torch.int32), best_epoch))
+        best_correct.copy_(torch.maximum(best_correct, vcorr))
+        ep_dev.add_(1)
+
+    graph = None
+    for ep in range(max_epochs):
+        if ft.lr_by_step and ft.steps_done + n_it > ft.n_sched:
+            raise RuntimeError("LR schedule shorter than the run")
+        perm.copy_(tr[torch.randperm(n_tr, device=dev, generator=gen)])
+        if not use_graph or ep == 0:
+            epoch_body()                                      # epoch 0 runs eagerly (kernel attributes, allocator warm-up)
+        else:
+            if graph is None:
+                graph = torch.cuda.CUDAGraph()
+                side = torch.cuda.Stream(dev)
+                side.wait_stream(torch.cuda.current_stream(dev))
+                with torch.cuda.stream(side):
+                    with torch.cuda.graph(graph, stream=side):
+                        epoch_body()
+                torch.cuda.current_stream(dev).wait_stream(side)
+            graph.replay()
+        ft.steps_done += n_it
     h = hist.cpu().numpy()                                    # the job's single host synchronisation
     with torch.no_grad():
         final = ft.flat.clone()
