@@ -452,7 +452,7 @@ def run_train(args, rank, world, local_rank):
     if rank == 0 and not args.no_extras:
         cpu = cpu_train_trials_per_s(64, os.cpu_count() or 1)
     line = {"metric": "FAST training trials/s (fwd+bwd+AdamW)", "value": value, "unit": "trials/s", "n_gpus": world, "steps": K,
-            "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": _train_dtype(FM),
             "data": "synthetic", "clocks": clocks.summary(),
             "config": {"workload": "FAST training step, production config, dropout 0.1 (BASELINE metric 'train fwd+bwd'; configs[0] batch = 64)",
                        "batch_per_gpu": B, "channels": 64, "samples": 795, "l2_policy": f"{nb} distinct resident batches rotated (> 126 MB)",
@@ -460,11 +460,37 @@ def run_train(args, rank, world, local_rank):
             "e2e": {"value": world * B * Ke / (e2e_ms * 1e-3), "unit": "trials/s", "h2d_bytes_per_step": B * BYTES_PER_TRIAL + B,
                     "d2h_bytes_per_step": 4, "steps": Ke},
             "gpu_launches": ft.LAUNCHES_TRAIN * K,
-            "roofline": {"kernel": "whole step (head_fwd + head_bwd dominate)", "bound": "fp32-fma (CUDA-core kernels)",
-                         "achieved": ach / world, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / world / fp32_peak, "traffic": None,
-                         "note": "direct-form training flops (SURVEY 8d: 1,140,087,744 per trial) / step time, per GPU"},
+            "roofline": _train_roofline(FM, ach / world, fp32_peak, peaks, B, ms / K),
             "cpu_baseline": cpu}
     _emit(line, dist, rank)
+
+
+def _train_dtype(FM):
+    p = FM.get_head_precision()
+    if FM.get_head_backward() == "tc" and p != "fp32":
+        return f"{p} split operands on tcgen05, f32 accumulate (f32 parameters, gradients and AdamW state)"
+    return "f32"
+
+
+def _train_roofline(FM, ach, fp32_peak, peaks, B, step_ms):
+    """Roofline of the whole training step: with the tensor-core head (forward, input-gradient chain, weight gradients all
+    tcgen05, split-bf16 operands) the bound is the tensor pipe; the step also moves ~16 MB of HBM per trial (saved
+    activations written by the forward and re-read by both backward kernels), so the HBM fraction is reported beside it."""
+    tc = FM.get_head_backward() == "tc" and FM.get_head_precision() != "fp32"
+    if not tc:
+        return {"kernel": "whole step (head_fwd + head_bwd dominate)", "bound": "fp32-fma (CUDA-core kernels)", "achieved": ach,
+                "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak, "traffic": None,
+                "note": "direct-form training flops (SURVEY 8d: 1,140,087,744 per trial) / step time, per GPU"}
+    tp = peaks.get("bf16_tflops_sustained", 1400.0)
+    hbm = peaks.get("hbm_gbs", 6500.0)
+    traffic = 16.4e9 * B / 1024                  # ncu --set full at batch 1024 (profiles/r01_train_tc_ncu_full.txt), linear in B
+    return {"kernel": "whole step (head_fwd_tc<SAVE> + head_dgrad_tc + head_wgrad_tc = 80 % of it)", "bound": "tensor",
+            "achieved": ach, "peak": tp, "unit": "TFLOP/s", "frac": ach / tp, "traffic": traffic,
+            "hbm_frac": traffic / (step_ms * 1e-3) / 1e9 / hbm,
+            "peak_source": ("bf16_tflops_sustained / hbm_gbs of MEASURED_PEAKS.json" if peaks else "fallback 1400 TFLOP/s, 6500 GB/s"),
+            "note": "achieved = direct-form training flops (SURVEY 8d: 1,140,087,744 per trial) / step time, per GPU; operands are "
+                    "2-3 bf16 terms each, so the tensor pipe issues 2-3x that; traffic = dram bytes of one step scaled from the "
+                    "batch-1024 ncu capture"}
 
 
 def cpu_train_trials_per_s(batch, threads):
@@ -510,7 +536,7 @@ def run_preprocess(args, rank, world, local_rank):
     def step():
         out = None
         for x in xs:
-            out = F.resample_poly(F.sosfiltfilt(sos, x, out_dtype=torch.float64), 4, 5, out_dtype=torch.float32)
+            out = F.sosfiltfilt_resample(sos, x, 4, 5, out_dtype=torch.float32)    # one fused kernel per subject block
         return out
 
     K, W = args.steps, args.warmup
@@ -530,14 +556,15 @@ def run_preprocess(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize(dev)
     ms = _max_over_ranks(e0.elapsed_time(e1), dist, dev)
-    # the filter kernel alone (dominant), f32 in -> f64 out as the chain uses it
+    # the step IS the dominant kernel (one fused launch per subject block); the unfused two-kernel chain beside it
+    filt_ms = e0.elapsed_time(e1) / (K * max(1, len(xs)))
     f0.record()
     for _ in range(K):
         for x in xs:
-            F.sosfiltfilt(sos, x, out_dtype=torch.float64)
+            F.resample_poly(F.sosfiltfilt(sos, x, out_dtype=torch.float64), 4, 5, out_dtype=torch.float32)
     f1.record()
     torch.cuda.synchronize(dev)
-    filt_ms = f0.elapsed_time(f1) / (K * max(1, len(xs)))
+    chain_ms = f0.elapsed_time(f1) / (K * max(1, len(xs)))
     total_trials = 15 * n_tr
     value = total_trials * K / (ms * 1e-3)
     # end to end from pinned host memory
@@ -547,13 +574,21 @@ def run_preprocess(args, rank, world, local_rank):
     e0.record()
     for xi, oi in zip(xh, outh):
         xd = xi.to(dev, non_blocking=True)
-        oi.copy_(F.resample_poly(F.sosfiltfilt(sos, xd, out_dtype=torch.float64), 4, 5, out_dtype=torch.float32), non_blocking=True)
+        oi.copy_(F.sosfiltfilt_resample(sos, xd, 4, 5, out_dtype=torch.float32), non_blocking=True)
     e1.record()
     torch.cuda.synchronize(dev)
     e2e_ms = _max_over_ranks(e0.elapsed_time(e1), dist, dev)
     peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
     hbm = peaks.get("hbm_gbs", 6500.0)
-    alg = n_tr * 64 * 795 * (4 + 8)                                     # f32 read + f64 write per launch
+    alg = n_tr * 64 * (795 + 636) * 4                                   # f32 read + f32 resampled write per launch
+    # fp64 work per row as the reference arithmetic defines it (2 passes x 4 sections x 9 flop per extended sample)
+    # plus the 26-tap polyphase dot products; the chunked scan executes ~2.6x the recursion flops (two sweeps + the scan)
+    fp64_alg = n_tr * 64 * (72.0 * (795 + 54) + 2.0 * 26 * 636)
+    fp64_peak = 148 * 64 * 2 * (peaks.get("sm_max_mhz", 1965.0) * 1e6) / 1e12      # 16 DFMA lanes x 4 sub-partitions per SM
+    traffic = None
+    tr_path = os.path.join(ROOT, "profiles", "filter_traffic.json")
+    if os.path.exists(tr_path):
+        traffic = json.load(open(tr_path)).get("sosfiltfilt_resample@400x64x795", {}).get("dram_bytes")
     cpu = None
     if rank == 0:
         nc = 2
@@ -572,10 +607,16 @@ def run_preprocess(args, rank, world, local_rank):
                        "parallelism": f"subjects sharded x{world}, no collective"},
             "e2e": {"value": total_trials / (e2e_ms * 1e-3),
                     "unit": "trials/s", "h2d_bytes_per_step": len(subs) * n_tr * 64 * 795 * 4, "d2h_bytes_per_step": len(subs) * n_tr * 64 * 636 * 4},
-            "gpu_launches": 2 * len(xs) * K,
-            "roofline": {"kernel": "sosfiltfilt_kernel", "bound": "hbm", "achieved": alg / (filt_ms * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
-                         "frac": alg / (filt_ms * 1e-3) / 1e9 / hbm, "traffic": None, "ms_per_launch": filt_ms,
-                         "algorithmic_bytes_per_launch": alg},
+            "gpu_launches": len(xs) * K,
+            "roofline": {"kernel": "sosfiltfilt_resample_kernel<4,4,5,26,2,float,float>", "bound": "hbm",
+                         "achieved": alg / (filt_ms * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
+                         "frac": alg / (filt_ms * 1e-3) / 1e9 / hbm, "traffic": traffic, "ms_per_launch": filt_ms,
+                         "algorithmic_bytes_per_launch": alg,
+                         "fp64_pipe": {"achieved": fp64_alg / (filt_ms * 1e-3) / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
+                                       "frac": fp64_alg / (filt_ms * 1e-3) / 1e12 / fp64_peak},
+                         "two_kernel_chain_ms": chain_ms,
+                         "note": "the 1e-5 parity bar forces an fp64 recursion (SURVEY 7.3-h), so the kernel sits on the FP64 pipe, "
+                                 "not on HBM: ncu shows sm__pipe_fp64_cycles_active ~70 % (profiles/), dram < 15 %"},
             "cpu_baseline": cpu}
     _emit(line, dist, rank)
 
@@ -657,7 +698,9 @@ def run_stress(args, rank, world, local_rank):
     else:
         dist.init_process_group("nccl", device_id=dev)
     from fast.models import FAST
+    from fast.models import fast as FM
     from fast.train import DataParallelTrainer
+    FM.set_head_precision(args.head_precision)
     cfg = prod_cfg()
     cfg.seq_len = 4000
     B, K, W = args.batch, args.steps, args.warmup
@@ -690,18 +733,20 @@ def run_stress(args, rank, world, local_rank):
     upd_ms = e0.elapsed_time(e1) / K if upd else 0.0
     loss, _ = ft.global_loss_and_correct()
     flop = 2.0 * (31 * (38_793_216 + 75_067_392) + 3 * 1_564_832) * 1.0
+    pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    tensor_peak = (json.load(open(pk)) if os.path.exists(pk) else {}).get("bf16_tflops_sustained", 1400.0)
     line = {"metric": "FAST stress training trials/s (64 ch x 4000 samples, data-parallel)", "value": world * B * K / (ms * 1e-3),
             "unit": "trials/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "clocks": clocks.summary(),
+            "scaling": "weak", "vs_baseline": None, "dtype": _train_dtype(FM), "data": "synthetic", "clocks": clocks.summary(),
             "config": {"workload": "BASELINE configs[4]: seq_len 4000 (31 windows, 32 tokens), DP", "batch_per_gpu": B,
                        "global_batch": B * world, "reduce": args.reduce if world > 1 else "none",
                        "l2_policy": f"input {B * 64 * 4000 * 4 / 1e9:.2f} GB per step > 126 MB L2",
                        "parallelism": f"dp{world}: one flat 767 KB gradient exchange per step"},
             "exchange_plus_update_ms": upd_ms, "loss": loss,
             "e2e": None, "gpu_launches": 9 * K,
-            "roofline": {"kernel": "whole step", "bound": "fp32-fma", "achieved": flop * B * K / (ms * 1e-3) / 1e12,
-                         "peak": 148 * 128 * 2 * 1.965e9 / 1e12, "unit": "TFLOP/s",
-                         "frac": flop * B * K / (ms * 1e-3) / 1e12 / (148 * 128 * 2 * 1.965e9 / 1e12), "traffic": None}}
+            "roofline": {"kernel": "whole step (tcgen05 head kernels)", "bound": "tensor", "achieved": flop * B * K / (ms * 1e-3) / 1e12,
+                         "peak": tensor_peak, "unit": "TFLOP/s", "frac": flop * B * K / (ms * 1e-3) / 1e12 / tensor_peak, "traffic": None,
+                         "note": "direct-form training flops per trial / step time, per GPU, against bf16_tflops_sustained"}}
     if rank == 0:
         print(json.dumps(line), flush=True)
     dist.destroy_process_group()

@@ -39,8 +39,28 @@ __device__ __forceinline__ double cascade_step(const SosParams<NS>& p, double (&
 }
 
 // one direction of the filtfilt over buf[0..N): REV mirrors the index.  In place.
+// impulse-response table of the cascade state: G[n] = state n steps after a unit sample entered a zero-state cascade.
+// The end state of a chunk run from the zero state is then  r = sum_q x[q] * G[chunk-1-q]  -- 2*NS independent fmas per
+// sample instead of the 5*NS dependent ones of the recursion (pass A is FP64-pipe bound).  Built once per CTA.
+template <int NS>
+__device__ __forceinline__ void build_impulse_table(const SosParams<NS>& p, double* G, int chunk) {
+    constexpr int SD = 2 * NS;
+    if (threadIdx.x == 0) {
+        double z[SD];
+#pragma unroll
+        for (int i = 0; i < SD; ++i) z[i] = 0.0;
+        for (int n = 0; n < chunk; ++n) {
+            cascade_step<NS>(p, z, n == 0 ? 1.0 : 0.0);
+#pragma unroll
+            for (int i = 0; i < SD; ++i) G[n * SD + i] = z[i];
+        }
+    }
+    __syncthreads();
+}
+
 template <int NS, bool REV>
-__device__ __forceinline__ void scan_direction(const SosParams<NS>& p, double* buf, int N, int chunk, int lane) {
+__device__ __forceinline__ void scan_direction(const SosParams<NS>& p, const double* __restrict__ G, double* buf, int N, int chunk,
+                                               int lane) {
     constexpr int SD = 2 * NS;
     const int p0 = lane * chunk;
     auto phys = [&](int q) { return REV ? N - 1 - q : q; };
@@ -51,13 +71,26 @@ __device__ __forceinline__ void scan_direction(const SosParams<NS>& p, double* b
         init[2 * s] = lane == 0 ? p.zi[s][0] * first : 0.0;
         init[2 * s + 1] = lane == 0 ? p.zi[s][1] * first : 0.0;
     }
+    // pass A: end state of this chunk from the zero state (impulse-table dot products) ...
 #pragma unroll
-    for (int i = 0; i < SD; ++i) z[i] = init[i];
-    // pass A: end state of this chunk from (zero | initial-condition) state
+    for (int i = 0; i < SD; ++i) z[i] = 0.0;
     for (int q = 0; q < chunk; ++q) {
         const int pq = p0 + q;
         const double v = pq < N ? buf[phys(pq)] : 0.0;
-        cascade_step<NS>(p, z, v);
+        const double* g = G + (chunk - 1 - q) * SD;
+#pragma unroll
+        for (int i = 0; i < SD; ++i) z[i] = fma(v, g[i], z[i]);
+    }
+    // ... plus, in lane 0, the zero-input response of the steady-state initial condition: M_chunk * init
+    // (the cascade is feed-forward: section s never sees the state of a later section, so M and its powers are block lower
+    // triangular and the products skip the zero blocks)
+#pragma unroll
+    for (int i = 0; i < SD; ++i) {
+        double acc = z[i];
+#pragma unroll
+        for (int j = 0; j < SD; ++j)
+            if ((j >> 1) <= (i >> 1)) acc = fma(p.P[0][i][j], init[j], acc);
+        z[i] = acc;
     }
     // inclusive scan over chunks: E_j = sum_{i<=j} M^(j-i) r_i
 #pragma unroll
@@ -66,14 +99,16 @@ __device__ __forceinline__ void scan_direction(const SosParams<NS>& p, double* b
         double up[SD];
 #pragma unroll
         for (int i = 0; i < SD; ++i) up[i] = __shfl_up_sync(0xffffffffu, z[i], d);
-        if (lane >= d) {
+        // branch-free: lanes below d receive their own value from the shuffle and simply add nothing
 #pragma unroll
-            for (int i = 0; i < SD; ++i) {
-                double acc = z[i];
+        for (int j = 0; j < SD; ++j) up[j] = lane >= d ? up[j] : 0.0;
 #pragma unroll
-                for (int j = 0; j < SD; ++j) acc = fma(p.P[k][i][j], up[j], acc);
-                z[i] = acc;
-            }
+        for (int i = 0; i < SD; ++i) {
+            double acc = z[i];
+#pragma unroll
+            for (int j = 0; j < SD; ++j)
+                if ((j >> 1) <= (i >> 1)) acc = fma(p.P[k][i][j], up[j], acc);
+            z[i] = acc;
         }
     }
     // start state of chunk j = end state of chunk j-1
@@ -83,24 +118,27 @@ __device__ __forceinline__ void scan_direction(const SosParams<NS>& p, double* b
         z[i] = lane == 0 ? init[i] : prev;
     }
     __syncwarp();
-    // pass B: true outputs
+    // pass B: true outputs.  Branch-free body (only the store is predicated): inside a divergent region the compiler reloads
+    // every filter coefficient from the constant bank on every sample (12 LDCU per 24 FP64 instructions, measured with ncu).
+    // Lanes past the end of the row (the last lane's tail) run on clamped addresses; their state is never used.
     for (int q = 0; q < chunk; ++q) {
         const int pq = p0 + q;
-        if (pq < N) {
-            const int a = phys(pq);
-            buf[a] = cascade_step<NS>(p, z, buf[a]);
-        }
+        const int a = phys(pq < N ? pq : N - 1);
+        const double out = cascade_step<NS>(p, z, buf[a]);
+        if (pq < N) buf[a] = out;
     }
     __syncwarp();
 }
 
 template <int NS, typename XT, typename YT>
-__global__ void __launch_bounds__(FILT_WARPS * 32) sosfiltfilt_kernel(const __grid_constant__ SosParams<NS> p,
+__global__ void __launch_bounds__(FILT_WARPS * 32, 4) sosfiltfilt_kernel(const __grid_constant__ SosParams<NS> p,
                                                                       const XT* __restrict__ x, YT* __restrict__ y,
                                                                       int64_t rows, int T, int edge, int chunk,
                                                                       int warps_per_cta) {
     extern __shared__ __align__(16) double fsm[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    double* G = fsm + (size_t)warps_per_cta * (32 * chunk);
+    build_impulse_table<NS>(p, G, chunk);
     if (warp >= warps_per_cta) return;
     const int N = T + 2 * edge;
     double* buf = fsm + (size_t)warp * (32 * chunk);
@@ -116,8 +154,8 @@ __global__ void __launch_bounds__(FILT_WARPS * 32) sosfiltfilt_kernel(const __gr
             }
         }
         __syncwarp();
-        scan_direction<NS, false>(p, buf, N, chunk, lane);
-        scan_direction<NS, true>(p, buf, N, chunk, lane);
+        scan_direction<NS, false>(p, G, buf, N, chunk, lane);
+        scan_direction<NS, true>(p, G, buf, N, chunk, lane);
         YT* yr = y + row * T;
         for (int t = lane; t < T; t += 32) yr[t] = (YT)buf[edge + t];
         __syncwarp();
@@ -188,6 +226,124 @@ __global__ void __launch_bounds__(FILT_WARPS * 32) resample_poly_kernel(const XT
     }
 }
 
+// ---- phase-major polyphase resampler for a compile-time up/down (the 250 -> 200 Hz default) ------------------------------
+// y[j] = sum_i x[i] * h0[j*DOWN + c - i*UP] with h0 = the FIR without its leading zeros, c = UP*cq + CR.  Output j = UP*m + p
+// reads x[DOWN*m + cq + (p*DOWN+CR)/UP - k] * H[p][k], H[p][k] = h0[(p*DOWN+CR)%UP + k*UP].  One lane owns one m (UP
+// consecutive outputs): the UP phases share one window of x values (NTAP + BMAX shared-memory reads for UP*NTAP fmas instead
+// of one read per fma), lanes are DOWN doubles apart (conflict-free for odd DOWN), and every coefficient is a constant-bank
+// operand of the DFMA (H lives in the kernel parameter block, all indices compile-time), so the LSU pipe carries x only.
+template <int UP, int NTAP>
+struct RsFir {
+    double H[UP][NTAP];
+};
+
+// MB outputs-groups (m, m + 32, ...) per lane: every coefficient (one uniform constant-bank load each) feeds MB fmas
+template <int UP, int DOWN, int NTAP, int CR, int MB, typename YT>
+__device__ __forceinline__ void resample_group(const RsFir<UP, NTAP>& fir, const double* xs, YT* __restrict__ yr, int T_out, int cq,
+                                               int n_m, int m0) {
+    constexpr int BMAX = ((UP - 1) * DOWN + CR) / UP;
+    const double* xb[MB];
+    double acc[MB][UP];
+#pragma unroll
+    for (int u = 0; u < MB; ++u) {
+        const int m = m0 + 32 * u < n_m ? m0 + 32 * u : m0;      // a lane without this m recomputes its first (not stored)
+        xb[u] = xs + DOWN * m + cq + BMAX;                       // xs is readable (zeros) outside [0, T_in): pads at the callers
+#pragma unroll
+        for (int p = 0; p < UP; ++p) acc[u][p] = 0.0;
+    }
+#pragma unroll
+    for (int t = 0; t < NTAP + BMAX; ++t) {
+        // compiler fence every 6 taps: without it all NTAP + BMAX shared-memory reads are hoisted to the top (60 live doubles)
+        if (t % 6 == 0) asm volatile("" ::: "memory");
+        double xv[MB];
+#pragma unroll
+        for (int u = 0; u < MB; ++u) xv[u] = xb[u][-t];
+#pragma unroll
+        for (int p = 0; p < UP; ++p) {
+            const int k = t - (BMAX - (p * DOWN + CR) / UP);
+            if (k >= 0 && k < NTAP) {
+#pragma unroll
+                for (int u = 0; u < MB; ++u) acc[u][p] = fma(xv[u], fir.H[p][k], acc[u][p]);
+            }
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < MB; ++u) {
+        const int m = m0 + 32 * u;
+#pragma unroll
+        for (int p = 0; p < UP; ++p)
+            if (m < n_m && UP * m + p < T_out) yr[UP * m + p] = (YT)acc[u][p];
+    }
+}
+
+template <int UP, int DOWN, int NTAP, int CR, typename YT>
+__device__ __forceinline__ void resample_row_phases(const RsFir<UP, NTAP>& fir, const double* xs, YT* __restrict__ yr, int T_out,
+                                                    int cq, int lane) {
+    const int n_m = (T_out + UP - 1) / UP;
+    // MB = 1: two groups per lane (MB = 2) halve the uniform coefficient loads but push the fused kernel over its 64-register
+    // budget (4 CTAs per SM keep the FP64 pipe fed); measured slower
+    for (int m0 = lane; m0 < n_m; m0 += 32) resample_group<UP, DOWN, NTAP, CR, 1, YT>(fir, xs, yr, T_out, cq, n_m, m0);
+}
+
+template <int UP, int DOWN, int NTAP, int CR, typename XT, typename YT>
+__global__ void __launch_bounds__(FILT_WARPS * 32, 2) resample_phase_kernel(const __grid_constant__ RsFir<UP, NTAP> fir,
+                                                                         const XT* __restrict__ x, YT* __restrict__ y,
+                                                                         int64_t rows, int T_in, int T_out, int cq, int PL,
+                                                                         int PR, int warps_per_cta) {
+    extern __shared__ __align__(16) double fsm[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp >= warps_per_cta) return;
+    const int span = PL + T_in + PR;
+    double* xs = fsm + (size_t)warp * span + PL;
+    for (int i = lane; i < PL; i += 32) xs[-1 - i] = 0.0;
+    for (int i = lane; i < PR; i += 32) xs[T_in + i] = 0.0;
+    for (int64_t row = (int64_t)blockIdx.x * warps_per_cta + warp; row < rows; row += (int64_t)gridDim.x * warps_per_cta) {
+        const XT* xr = x + row * T_in;
+        for (int t = lane; t < T_in; t += 32) xs[t] = (double)xr[t];
+        __syncwarp();
+        resample_row_phases<UP, DOWN, NTAP, CR, YT>(fir, xs, y + row * T_out, T_out, cq, lane);
+        __syncwarp();
+    }
+}
+
+// sosfiltfilt and the resampler in one pass over the row: the fp64 filtered row never leaves shared memory (the two-kernel
+// chain writes and re-reads it through HBM: 16 of its 23 bytes per sample), and the resampler's shared-memory reads overlap
+// the filter's FP64-pipe-bound recursion of the other warps.
+template <int NS, int UP, int DOWN, int NTAP, int CR, typename XT, typename YT>
+__global__ void __launch_bounds__(FILT_WARPS * 32, 4) sosfiltfilt_resample_kernel(const __grid_constant__ SosParams<NS> p,
+                                                                               const __grid_constant__ RsFir<UP, NTAP> fir,
+                                                                               const XT* __restrict__ x, YT* __restrict__ y,
+                                                                               int64_t rows, int T, int edge, int chunk,
+                                                                               int warps_per_cta, int T_out, int cq) {
+    extern __shared__ __align__(16) double fsm[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    double* G = fsm + (size_t)warps_per_cta * (32 * chunk);
+    build_impulse_table<NS>(p, G, chunk);
+    if (warp >= warps_per_cta) return;
+    const int N = T + 2 * edge;
+    double* buf = fsm + (size_t)warp * (32 * chunk);
+    for (int64_t row = (int64_t)blockIdx.x * warps_per_cta + warp; row < rows; row += (int64_t)gridDim.x * warps_per_cta) {
+        const XT* xr = x + row * T;
+        for (int t = lane; t < T; t += 32) buf[edge + t] = (double)xr[t];
+        const XT x0 = xr[0], xl = xr[T - 1];
+        for (int i = lane; i < edge; i += 32) {
+            buf[i] = (double)(XT)((XT)2 * x0 - xr[edge - i]);
+            buf[edge + T + i] = (double)(XT)((XT)2 * xl - xr[T - 2 - i]);
+        }
+        __syncwarp();
+        scan_direction<NS, false>(p, G, buf, N, chunk, lane);
+        scan_direction<NS, true>(p, G, buf, N, chunk, lane);
+        // the resampler pads with zeros, not with the filtered extension
+        for (int i = lane; i < edge; i += 32) {
+            buf[i] = 0.0;
+            buf[edge + T + i] = 0.0;
+        }
+        __syncwarp();
+        resample_row_phases<UP, DOWN, NTAP, CR, YT>(fir, buf + edge, y + row * T_out, T_out, cq, lane);
+        __syncwarp();
+    }
+}
+
 // ---- host: transition-matrix powers -----------------------------------------------------------------------------
 template <int NS>
 static void fill_params(SosParams<NS>& p, const double* sos, int chunk) {
@@ -242,12 +398,12 @@ static int launch_sos(const void* x, void* y, int64_t rows, int T, const double*
     const int N = T + 2 * edge;
     const int chunk = ceil_div(N, 32);
     const size_t per_warp = (size_t)32 * chunk * sizeof(double);
-    int warps = (int)((220 * 1024) / per_warp);
+    int warps = (int)((220 * 1024 - (size_t)chunk * 2 * NS * sizeof(double)) / per_warp);
     if (warps < 1) return fail(-2, "row of %d samples does not fit the shared-memory resident filter", T);
     if (warps > FILT_WARPS) warps = FILT_WARPS;
     // keep >= 2 CTAs per SM resident when rows are short
     if (warps == FILT_WARPS && per_warp * FILT_WARPS > 110 * 1024) warps = FILT_WARPS / 2;
-    const size_t smem = per_warp * warps;
+    const size_t smem = per_warp * warps + (size_t)chunk * 2 * NS * sizeof(double);       // + the impulse table
     SosParams<NS> p;
     fill_params<NS>(p, sos, chunk);
     auto kern = sosfiltfilt_kernel<NS, XT, YT>;
@@ -286,6 +442,91 @@ static int launch_resample(const void* x, void* y, int64_t rows, int T_in, int T
     return check_launch("resample_poly");
 }
 
+// ---- host: the compile-time-ratio resampler (4/5, scipy's default FIR alignment) -------------------------------------------
+constexpr int RS_UP = 4, RS_DOWN = 5, RS_NTAP = 26, RS_CR = 2;
+struct RsPlan {
+    RsFir<RS_UP, RS_NTAP> fir;
+    int cq, PL, PR;
+};
+
+// true when (h, up, down, n_pre_remove) is the shape resample_phase_kernel is compiled for; fills the coefficient table
+static bool plan_phases(const double* h, int len_h, int up, int down, int npr, int T_in, int T_out, RsPlan& pl) {
+    if (h == nullptr || up != RS_UP || down != RS_DOWN) return false;
+    int lead = 0, L = len_h;
+    while (lead < len_h && h[lead] == 0.0) ++lead;
+    while (L > lead && h[L - 1] == 0.0) --L;
+    const int L0 = L - lead;
+    const long long c = (long long)npr * down - lead;
+    if (L0 < 1 || L0 > RS_UP * RS_NTAP || c < 0 || c % RS_UP != RS_CR || c / RS_UP > (1 << 20)) return false;
+    pl.cq = (int)(c / RS_UP);
+    for (int p = 0; p < RS_UP; ++p) {
+        const int r = (p * RS_DOWN + RS_CR) % RS_UP;
+        for (int k = 0; k < RS_NTAP; ++k) pl.fir.H[p][k] = r + k * RS_UP < L0 ? h[lead + r + k * RS_UP] : 0.0;
+    }
+    constexpr int BMAX = ((RS_UP - 1) * RS_DOWN + RS_CR) / RS_UP;
+    const int n_m = (T_out + RS_UP - 1) / RS_UP;
+    const int lo = pl.cq - (RS_NTAP - 1), hi = RS_DOWN * (n_m - 1) + pl.cq + BMAX;
+    pl.PL = lo < 0 ? -lo : 0;
+    pl.PR = hi > T_in - 1 ? hi - (T_in - 1) : 0;
+    return pl.PL <= 4096 && pl.PR <= 4096;
+}
+
+template <typename XT, typename YT>
+static int launch_resample_phases(const RsPlan& pl, const void* x, void* y, int64_t rows, int T_in, int T_out,
+                                  cudaStream_t st) {
+    const size_t per_warp = (size_t)(pl.PL + T_in + pl.PR) * sizeof(double);
+    int warps = (int)((100 * 1024) / per_warp);
+    if (warps < 1) return -2;
+    if (warps > FILT_WARPS) warps = FILT_WARPS;
+    const size_t smem = per_warp * warps;
+    auto kern = resample_phase_kernel<RS_UP, RS_DOWN, RS_NTAP, RS_CR, XT, YT>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return fail((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    int64_t grid = (rows + warps - 1) / warps;
+    if (grid > NUM_SMS * 8) grid = NUM_SMS * 8;
+    kern<<<(unsigned)grid, FILT_WARPS * 32, smem, st>>>(pl.fir, (const XT*)x, (YT*)y, rows, T_in, T_out, pl.cq, pl.PL, pl.PR, warps);
+    return check_launch("resample_poly (phase-major)");
+}
+
+// geometry of the fused kernel: the row buffer of the filter (T + 2*edge, rounded up to 32 chunks) must hold the resampler's pads
+static bool fused_geometry(int T, int edge, const RsPlan& pl, int& chunk, int& warps) {
+    const int N = T + 2 * edge;
+    chunk = ceil_div(N, 32);
+    if (pl.PL > edge || pl.PR > edge) return false;
+    const size_t per_warp = (size_t)32 * chunk * sizeof(double);
+    warps = (int)((220 * 1024 - (size_t)chunk * 2 * FILT_MAX_SEC * sizeof(double)) / per_warp);
+    if (warps < 1) return false;
+    if (warps > FILT_WARPS) warps = FILT_WARPS;
+    if (warps == FILT_WARPS && per_warp * FILT_WARPS > 110 * 1024) warps = FILT_WARPS / 2;
+    return true;
+}
+
+template <int NS, typename XT, typename YT>
+static int launch_fused(const RsPlan& pl, const void* x, void* y, int64_t rows, int T, int T_out, const double* sos, int edge,
+                        cudaStream_t st) {
+    int chunk, warps;
+    if (!fused_geometry(T, edge, pl, chunk, warps)) return fail(-3, "sosfiltfilt_resample: unsupported geometry");
+    const size_t smem = (size_t)32 * chunk * sizeof(double) * warps + (size_t)chunk * 2 * NS * sizeof(double);
+    SosParams<NS> p;
+    fill_params<NS>(p, sos, chunk);
+    auto kern = sosfiltfilt_resample_kernel<NS, RS_UP, RS_DOWN, RS_NTAP, RS_CR, XT, YT>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return fail((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    int64_t grid = (rows + warps - 1) / warps;
+    if (grid > NUM_SMS * 8) grid = NUM_SMS * 8;
+    kern<<<(unsigned)grid, FILT_WARPS * 32, smem, st>>>(p, pl.fir, (const XT*)x, (YT*)y, rows, T, edge, chunk, warps, T_out, pl.cq);
+    return check_launch("sosfiltfilt_resample");
+}
+
+template <int NS>
+static int dispatch_fused(const RsPlan& pl, const void* x, int xb, void* y, int yb, int64_t rows, int T, int T_out,
+                          const double* sos, int edge, cudaStream_t st) {
+    if (xb == 4 && yb == 4) return launch_fused<NS, float, float>(pl, x, y, rows, T, T_out, sos, edge, st);
+    if (xb == 4 && yb == 8) return launch_fused<NS, float, double>(pl, x, y, rows, T, T_out, sos, edge, st);
+    if (xb == 8 && yb == 4) return launch_fused<NS, double, float>(pl, x, y, rows, T, T_out, sos, edge, st);
+    return launch_fused<NS, double, double>(pl, x, y, rows, T, T_out, sos, edge, st);
+}
+
 }  // namespace fb
 
 using namespace fb;
@@ -311,14 +552,56 @@ extern "C" int fastb200_sosfiltfilt(const void* x, int x_bytes, void* y, int y_b
 
 extern "C" int fastb200_resample_poly(const void* x, int x_bytes, void* y, int y_bytes, int64_t rows, int T_in,
                                       int T_out, const double* h_dev, int len_h, int up, int down, int n_pre_remove,
-                                      void* stream) {
+                                      const double* h_host, void* stream) {
     FB_REQUIRE((x_bytes == 4 || x_bytes == 8) && (y_bytes == 4 || y_bytes == 8), "x / y must be fp32 or fp64");
     FB_REQUIRE(rows >= 0 && T_in >= 1 && T_out >= 1 && len_h >= 1 && up >= 1 && down >= 1 && n_pre_remove >= 0, "bad dims");
     FB_REQUIRE(len_h <= 4096, "FIR of %d taps is too long", len_h);
     if (rows == 0) return 0;
     cudaStream_t st = as_stream(stream);
+    RsPlan pl;
+    if (plan_phases(h_host, len_h, up, down, n_pre_remove, T_in, T_out, pl)) {
+        int rc;
+        if (x_bytes == 4 && y_bytes == 4) rc = launch_resample_phases<float, float>(pl, x, y, rows, T_in, T_out, st);
+        else if (x_bytes == 4 && y_bytes == 8) rc = launch_resample_phases<float, double>(pl, x, y, rows, T_in, T_out, st);
+        else if (x_bytes == 8 && y_bytes == 4) rc = launch_resample_phases<double, float>(pl, x, y, rows, T_in, T_out, st);
+        else rc = launch_resample_phases<double, double>(pl, x, y, rows, T_in, T_out, st);
+        if (rc != -2) return rc;                                    // -2: row too long for this kernel's staging, use the generic one
+    }
+    FB_REQUIRE(h_dev != nullptr, "h_dev is NULL");
     if (x_bytes == 4 && y_bytes == 4) return launch_resample<float, float>(x, y, rows, T_in, T_out, h_dev, len_h, up, down, n_pre_remove, st);
     if (x_bytes == 4 && y_bytes == 8) return launch_resample<float, double>(x, y, rows, T_in, T_out, h_dev, len_h, up, down, n_pre_remove, st);
     if (x_bytes == 8 && y_bytes == 4) return launch_resample<double, float>(x, y, rows, T_in, T_out, h_dev, len_h, up, down, n_pre_remove, st);
     return launch_resample<double, double>(x, y, rows, T_in, T_out, h_dev, len_h, up, down, n_pre_remove, st);
+}
+
+extern "C" int fastb200_sosfiltfilt_resample_supported(int T, int n_sections, int padlen, int T_out, const double* h_host,
+                                                       int len_h, int up, int down, int n_pre_remove) {
+    if (T < 1 || T <= padlen || padlen < 0 || n_sections < 1 || n_sections > FILT_MAX_SEC || T_out < 1 || len_h < 1) return 0;
+    RsPlan pl;
+    if (!plan_phases(h_host, len_h, up, down, n_pre_remove, T, T_out, pl)) return 0;
+    int chunk, warps;
+    return fused_geometry(T, padlen, pl, chunk, warps) ? 1 : 0;
+}
+
+extern "C" int fastb200_sosfiltfilt_resample(const void* x, int x_bytes, void* y, int y_bytes, int64_t rows, int T,
+                                             const double* sos_host, int n_sections, int padlen, int T_out,
+                                             const double* h_host, int len_h, int up, int down, int n_pre_remove,
+                                             void* stream) {
+    FB_REQUIRE(sos_host != nullptr && h_host != nullptr, "sos / h is NULL");
+    FB_REQUIRE(n_sections >= 1 && n_sections <= FILT_MAX_SEC, "n_sections=%d unsupported (1..%d)", n_sections, FILT_MAX_SEC);
+    FB_REQUIRE((x_bytes == 4 || x_bytes == 8) && (y_bytes == 4 || y_bytes == 8), "x / y must be fp32 or fp64");
+    FB_REQUIRE(rows >= 0 && T >= 1 && padlen >= 0 && T_out >= 1 && len_h >= 1, "bad rows / T / padlen / T_out / len_h");
+    FB_REQUIRE(T > padlen, "The length of the input vector x must be greater than padlen, which is %d.", padlen);
+    for (int s = 0; s < n_sections; ++s) FB_REQUIRE(sos_host[s * 6 + 3] != 0.0, "sos[%d, 3] (a0) is zero", s);
+    RsPlan pl;
+    if (!plan_phases(h_host, len_h, up, down, n_pre_remove, T, T_out, pl))
+        return fail(-3, "sosfiltfilt_resample: up/down/FIR shape not supported by the fused kernel (use the two-call chain)");
+    if (rows == 0) return 0;
+    cudaStream_t st = as_stream(stream);
+    switch (n_sections) {
+        case 1: return dispatch_fused<1>(pl, x, x_bytes, y, y_bytes, rows, T, T_out, sos_host, padlen, st);
+        case 2: return dispatch_fused<2>(pl, x, x_bytes, y, y_bytes, rows, T, T_out, sos_host, padlen, st);
+        case 3: return dispatch_fused<3>(pl, x, x_bytes, y, y_bytes, rows, T, T_out, sos_host, padlen, st);
+        default: return dispatch_fused<4>(pl, x, x_bytes, y, y_bytes, rows, T, T_out, sos_host, padlen, st);
+    }
 }

@@ -76,7 +76,12 @@ SIGNATURES = {
     "fastb200_sosfiltfilt": (C.c_int, [_P, C.c_int, _P, C.c_int, C.c_int64, C.c_int, C.POINTER(C.c_double), C.c_int,
                                        C.c_int, _P]),
     "fastb200_resample_poly": (C.c_int, [_P, C.c_int, _P, C.c_int, C.c_int64, C.c_int, C.c_int, _P, C.c_int, C.c_int,
-                                         C.c_int, C.c_int, _P]),
+                                         C.c_int, C.c_int, C.POINTER(C.c_double), _P]),
+    "fastb200_sosfiltfilt_resample_supported": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.c_int,
+                                                          C.c_int, C.c_int, C.c_int]),
+    "fastb200_sosfiltfilt_resample": (C.c_int, [_P, C.c_int, _P, C.c_int, C.c_int64, C.c_int, C.POINTER(C.c_double), C.c_int,
+                                                C.c_int, C.c_int, C.POINTER(C.c_double), C.c_int, C.c_int, C.c_int, C.c_int,
+                                                _P]),
 }
 
 _lib = None

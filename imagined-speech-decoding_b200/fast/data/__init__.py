@@ -17,7 +17,7 @@ from .preprocess import (
     load_subject_train_val,
     trials_from_mat,
 )
-from .filters import bandpass_sos, sosfiltfilt, resample_poly, bandpass_resample
+from .filters import bandpass_sos, sosfiltfilt, resample_poly, sosfiltfilt_resample, bandpass_resample
 
 __all__ = [
     "BasicDataset",
@@ -38,5 +38,6 @@ __all__ = [
     "bandpass_sos",
     "sosfiltfilt",
     "resample_poly",
+    "sosfiltfilt_resample",
     "bandpass_resample",
 ]

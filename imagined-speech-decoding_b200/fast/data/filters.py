@@ -81,41 +81,85 @@ def _kaiser_lowpass(up, down, beta=5.0):
 _FIR_CACHE = {}
 
 
-def resample_poly(x, up, down, window=None, out_dtype=None):
-    """Polyphase resampling by ``up/down`` along the last axis of a CUDA tensor with zero-padded edges
-    (``scipy.signal.resample_poly(x, up, down, axis=-1)`` defaults).  ``window``: optional 1-D FIR (already designed
-    for the reduced up/down, unity DC gain before the ``up`` scaling)."""
+def _fir_plan(device, up, down, window):
+    """(h_host with scipy's leading zero pad, h_dev, n_pre_remove) for the reduced ratio; cached per device."""
+    key = (device, up, down, None if window is None else np.asarray(window, dtype=np.float64).tobytes())
+    plan = _FIR_CACHE.get(key)
+    if plan is None:
+        h = _kaiser_lowpass(up, down) if window is None else np.asarray(window, dtype=np.float64) * up
+        half = (len(h) - 1) // 2
+        n_pre_pad = down - half % down
+        n_pre_remove = (half + n_pre_pad) // down
+        h_host = np.ascontiguousarray(np.concatenate([np.zeros(n_pre_pad), h]))
+        plan = (h_host, torch.from_numpy(h_host).to(device), n_pre_remove)
+        _FIR_CACHE[key] = plan
+    return plan
+
+
+def _reduce_ratio(up, down):
     up, down = int(up), int(down)
     if up < 1 or down < 1:
         raise ValueError("up and down must be >= 1")
     g = math.gcd(up, down)
-    up, down = up // g, down // g
+    return up // g, down // g
+
+
+def resample_poly(x, up, down, window=None, out_dtype=None):
+    """Polyphase resampling by ``up/down`` along the last axis of a CUDA tensor with zero-padded edges
+    (``scipy.signal.resample_poly(x, up, down, axis=-1)`` defaults).  ``window``: optional 1-D FIR (already designed
+    for the reduced up/down, unity DC gain before the ``up`` scaling)."""
+    up, down = _reduce_ratio(up, down)
     x = _as_rows(x)
     odt = _out_dtype(x, out_dtype)
     if up == down == 1:
         return x.to(odt, copy=True)
     T_in = x.shape[-1]
     T_out = -(-T_in * up // down)
-    h = _kaiser_lowpass(up, down) if window is None else np.asarray(window, dtype=np.float64) * up
-    half = (len(h) - 1) // 2
-    n_pre_pad = down - half % down
-    n_pre_remove = (half + n_pre_pad) // down
-    key = (x.device, up, down, None if window is None else h.tobytes())
-    h_dev = _FIR_CACHE.get(key)
-    if h_dev is None:
-        h_dev = torch.from_numpy(np.concatenate([np.zeros(n_pre_pad), h])).to(x.device)
-        _FIR_CACHE[key] = h_dev
+    h_host, h_dev, n_pre_remove = _fir_plan(x.device, up, down, window)
     y = torch.empty(*x.shape[:-1], T_out, device=x.device, dtype=odt)
     rows = x.numel() // T_in if T_in else 0
     with torch.cuda.device(x.device):
         N.check(N.lib().fastb200_resample_poly(N.ptr(x), x.element_size(), N.ptr(y), y.element_size(), rows, T_in, T_out,
                                                N.ptr(h_dev), h_dev.numel(), up, down, n_pre_remove,
+                                               h_host.ctypes.data_as(C.POINTER(C.c_double)),
                                                N.stream_ptr(x.device)), "resample_poly")
     return y
 
 
+def sosfiltfilt_resample(sos, x, up, down, padlen=None, window=None, out_dtype=None):
+    """``resample_poly(sosfiltfilt(sos, x), up, down)`` with a float64 intermediate.  Where the fused kernel supports
+    the shape (4/5 with the default FIR) the filtered row never leaves shared memory; other shapes run the two
+    kernels back to back.  Results are those of the two-call chain either way."""
+    sos = np.ascontiguousarray(sos, dtype=np.float64)
+    if sos.ndim != 2 or sos.shape[1] != 6:
+        raise ValueError("sos must be shape (n_sections, 6)")
+    up, down = _reduce_ratio(up, down)
+    x = _as_rows(x)
+    odt = _out_dtype(x, out_dtype)
+    T = x.shape[-1]
+    edge = default_padlen(sos) if padlen is None else int(padlen)
+    if T <= edge:
+        raise ValueError(f"The length of the input vector x must be greater than padlen, which is {edge}.")
+    T_out = -(-T * up // down)
+    L = N.lib()
+    if not (up == down == 1):
+        h_host, _, n_pre_remove = _fir_plan(x.device, up, down, window)
+        hp = h_host.ctypes.data_as(C.POINTER(C.c_double))
+        if sos.shape[0] <= 4 and L.fastb200_sosfiltfilt_resample_supported(T, sos.shape[0], edge, T_out, hp, len(h_host), up, down,
+                                                                          n_pre_remove):
+            y = torch.empty(*x.shape[:-1], T_out, device=x.device, dtype=odt)
+            rows = x.numel() // T
+            with torch.cuda.device(x.device):
+                N.check(L.fastb200_sosfiltfilt_resample(N.ptr(x), x.element_size(), N.ptr(y), y.element_size(), rows, T,
+                                                        sos.ctypes.data_as(C.POINTER(C.c_double)), sos.shape[0], edge, T_out,
+                                                        hp, len(h_host), up, down, n_pre_remove, N.stream_ptr(x.device)),
+                        "sosfiltfilt_resample")
+            return y
+    return resample_poly(sosfiltfilt(sos, x, padlen=edge, out_dtype=torch.float64), up, down, window=window, out_dtype=odt)
+
+
 def bandpass_resample(x, fs=250.0, low=4.0, high=40.0, order=4, up=4, down=5, out_dtype=torch.float32):
     """The preprocessing chain of BASELINE.json config 3: order-``order`` Butterworth ``low``-``high`` Hz zero-phase
-    band-pass, then ``up/down`` polyphase resampling (250 -> 200 Hz by default).  The intermediate stays float64."""
-    y = sosfiltfilt(bandpass_sos(order, low, high, fs), x, out_dtype=torch.float64)
-    return resample_poly(y, up, down, out_dtype=out_dtype)
+    band-pass, then ``up/down`` polyphase resampling (250 -> 200 Hz by default).  The intermediate stays float64
+    (in shared memory where the fused kernel applies)."""
+    return sosfiltfilt_resample(bandpass_sos(order, low, high, fs), x, up, down, out_dtype=out_dtype)

@@ -236,9 +236,25 @@ int fastb200_sosfiltfilt(const void* x, int x_bytes, void* y, int y_bytes, int64
 /*
  * scipy.signal.resample_poly(x, up, down, axis=-1) with padtype='constant' (zero) edges.  h: DEVICE pointer to
  * the already up-scaled, pre-padded fp64 FIR (len_h taps); y[j] = sum_i x[i] * h[(j+n_pre_remove)*down - i*up].
+ * h_host: the same FIR in HOST memory, or NULL.  When it is given and (up, down) = (4, 5) with scipy's default FIR
+ * alignment (the 250 -> 200 Hz case), a phase-major kernel runs whose coefficients sit in the kernel parameter block
+ * (constant-bank operands); any other shape runs the generic kernel from h_dev.
  */
 int fastb200_resample_poly(const void* x, int x_bytes, void* y, int y_bytes, int64_t rows, int T_in, int T_out,
-                           const double* h_dev, int len_h, int up, int down, int n_pre_remove, void* stream);
+                           const double* h_dev, int len_h, int up, int down, int n_pre_remove, const double* h_host,
+                           void* stream);
+/*
+ * The chain resample_poly(sosfiltfilt(sos, x), up, down) in ONE kernel: the fp64 filtered row stays in shared
+ * memory (the two-call chain writes and re-reads it through HBM).  Same arithmetic, same results as the two calls
+ * with an fp64 intermediate.  x (rows, T), y (rows, T_out); sos_host / h_host: HOST pointers.  Supported shapes:
+ * fastb200_sosfiltfilt_resample_supported(...) == 1 (up/down = 4/5, default FIR alignment, padlen >= the
+ * resampler's edge reach); otherwise the call returns -3 and the caller uses the two-call chain.
+ */
+int fastb200_sosfiltfilt_resample_supported(int T, int n_sections, int padlen, int T_out, const double* h_host,
+                                            int len_h, int up, int down, int n_pre_remove);
+int fastb200_sosfiltfilt_resample(const void* x, int x_bytes, void* y, int y_bytes, int64_t rows, int T,
+                                  const double* sos_host, int n_sections, int padlen, int T_out,
+                                  const double* h_host, int len_h, int up, int down, int n_pre_remove, void* stream);
 
 #ifdef __cplusplus
 }

@@ -28,7 +28,7 @@ def test_header_declares_the_documented_surface():
     syms = _header_symbols()
     for must in ("fastb200_window_gather", "fastb200_head_fwd", "fastb200_head_bwd", "fastb200_transformer_fwd",
                  "fastb200_transformer_bwd", "fastb200_ce_fwd_bwd", "fastb200_adamw_flat", "fastb200_sosfiltfilt",
-                 "fastb200_resample_poly", "fastb200_trials_from_mat", "fastb200_last_error"):
+                 "fastb200_resample_poly", "fastb200_sosfiltfilt_resample", "fastb200_sosfiltfilt_resample_supported", "fastb200_trials_from_mat", "fastb200_last_error"):
         assert must in syms
 
 

@@ -328,6 +328,44 @@ def test_resample_poly_vs_scipy_golden(filter_golden):
     assert out.dtype == torch.float32 and rel_err(out, g["y_resample_4_5"]) < TOL_FILTER
 
 
+def test_fused_filter_resample_equals_the_two_call_chain(filter_golden):
+    """The one-kernel band-pass + 4/5 resample (filtered row stays in shared memory) gives the bits of the two-kernel chain
+    with its float64 intermediate; the phase-major 4/5 resampler agrees with the generic kernel (forced by a custom
+    window of another alignment) and with the oracle on ragged lengths; unsupported shapes fall back to two calls."""
+    from fast.data import resample_poly, sosfiltfilt, sosfiltfilt_resample
+    from fast.data.filters import _kaiser_lowpass
+    g = filter_golden
+    sos = g["sos"]
+    x = torch.from_numpy(g["x"]).cuda()
+    for odt in (torch.float32, torch.float64):
+        fused = sosfiltfilt_resample(sos, x, 4, 5, out_dtype=odt)
+        chain = resample_poly(sosfiltfilt(sos, x, out_dtype=torch.float64), 4, 5, out_dtype=odt)
+        assert fused.dtype == odt and torch.equal(fused, chain)
+    assert rel_err(sosfiltfilt_resample(sos, x, 4, 5, out_dtype=torch.float64), g["y_resample_4_5"]) < 1e-9
+    xd = x.double()
+    assert torch.equal(sosfiltfilt_resample(sos, xd, 4, 5), resample_poly(sosfiltfilt(sos, xd), 4, 5))
+    # fewer sections, ragged lengths (T_out not a multiple of 4), one row
+    for T in (100, 333, 794, 1001):
+        xr = torch.randn(3, 5, T, device='cuda', dtype=torch.float64, generator=torch.Generator(device='cuda').manual_seed(T))
+        ref = FO.resample_poly(FO.sosfiltfilt(g["sos_lp"], xr.cpu().numpy()), 4, 5)
+        out = sosfiltfilt_resample(g["sos_lp"], xr, 4, 5)
+        assert out.shape[-1] == -(-T * 4 // 5) and rel_err(out, ref) < 1e-9, T
+        assert rel_err(resample_poly(xr, 4, 5), FO.resample_poly(xr.cpu().numpy(), 4, 5)) < 1e-11, T
+    # a user FIR of a different length / alignment takes the generic kernel: same answer as scipy
+    from scipy import signal
+    y = torch.from_numpy(g["y_sosfiltfilt"]).cuda()
+    for ntaps in (61, 63, 141):           # 61: phase-major kernel (same alignment as the default); 63, 141: generic kernel
+        w = signal.firwin(ntaps, 0.2, window=('kaiser', 5.0))
+        ref = signal.resample_poly(g["y_sosfiltfilt"], 4, 5, axis=-1, window=w)
+        assert rel_err(resample_poly(y, 4, 5, window=w), ref) < 1e-11, ntaps
+    # the default FIR passed explicitly is the default path
+    assert torch.equal(resample_poly(y, 4, 5, window=_kaiser_lowpass(4, 5) / 4), resample_poly(y, 4, 5))
+    # unsupported by the fused kernel (ratio 125/128; padlen 0): two-call chain, same contract
+    assert rel_err(sosfiltfilt_resample(sos, x, 125, 128, out_dtype=torch.float64), g["y_resample_125_128"]) < 1e-9
+    p0 = sosfiltfilt_resample(sos, xd, 4, 5, padlen=0)
+    assert torch.equal(p0, resample_poly(sosfiltfilt(sos, xd, padlen=0), 4, 5))
+
+
 def test_filter_properties_at_scale(filter_golden):
     """BASELINE config-3 sized batch: linearity and time-reversal symmetry of the zero-phase filter."""
     from fast.data import sosfiltfilt
