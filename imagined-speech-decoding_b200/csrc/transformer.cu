@@ -9,6 +9,7 @@
 // LayerNorm / softmax reductions are warp shuffles; dropout masks come from a counter-based generator so the
 // backward kernel regenerates them instead of storing them.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace fb {
 
@@ -34,36 +35,45 @@ struct DropCtx {
 };
 
 // ---- shared-memory resident building blocks (all threads of the CTA call these; R = live rows) --------------
-__device__ __forceinline__ void stage_w(float* dst, const float* __restrict__ src, int rows, int cols) {
+// Asynchronous (cp.async, 4 bytes: the padded pitch breaks 16-byte alignment): a load -> store loop through registers
+// serialises on the L2 latency of every element (the compiler cannot hoist the loads over the shared-memory stores), which
+// cost ~12 us per block at one trial per CTA.  Callers run stage_wait() + __syncthreads() before the first use.
+__device__ __noinline__ void stage_w(float* dst, const float* __restrict__ src, int rows, int cols) {
     const int ld = cols + 1;                                   // odd-ish pitch: conflict free both ways
+    int r = threadIdx.x / cols, c = threadIdx.x - r * cols;
+    const int dr = TR_THREADS / cols, dc = TR_THREADS - dr * cols;
     for (int i = threadIdx.x; i < rows * cols; i += TR_THREADS) {
-        const int r = i / cols, c = i - r * cols;
-        dst[r * ld + c] = __ldg(src + i);
+        const unsigned d = (unsigned)__cvta_generic_to_shared(dst + r * ld + c);
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(src + i) : "memory");
+        r += dr; c += dc;
+        if (c >= cols) { c -= cols; ++r; }
     }
 }
+__device__ __forceinline__ void stage_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
-// Y[r][j] = (RES ? Y[r][j] : 0) + post( act(b[j] + sum_i X[r][i] W[j][i]) )   -- 4 rows per thread
-template <int ACT, bool RES, typename Post>
-__device__ __forceinline__ void linear_fwd(const float* Xs, int ldx, const float* Ws, int Din, int Dout,
-                                           const float* __restrict__ bias, float* Ys, int ldy, int R,
-                                           float* pre_s, Post post) {
+// Y[r][j] = (RES ? Y[r][j] : 0) + post( act(b[j] + sum_i X[r][i] W[j][i]) )   -- RPT rows per thread.
+// bias may live in shared memory (the per-block vectors staged by stage_block) or in global memory: plain loads.
+template <int ACT, bool RES, int RPT, typename Post>
+__device__ __forceinline__ void linear_fwd_rpt(const float* Xs, int ldx, const float* Ws, int Din, int Dout, const float* bias,
+                                               float* Ys, int ldy, int R, float* pre_s, Post post) {
     const int ldw = Din + 1;
-    const int RG = (R + 3) >> 2;
+    const int RG = (R + RPT - 1) / RPT;
     for (int idx = threadIdx.x; idx < RG * Dout; idx += TR_THREADS) {
-        const int j = idx % Dout, r0 = (idx / Dout) << 2;
-        const float b = bias ? __ldg(bias + j) : 0.f;
-        float acc[4] = {b, b, b, b};
-        const float* xr[4];
+        const int j = idx % Dout, r0 = (idx / Dout) * RPT;
+        const float b = bias ? bias[j] : 0.f;
+        float acc[RPT];
+        const float* xr[RPT];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) xr[q] = Xs + min(r0 + q, R - 1) * ldx;
+        for (int q = 0; q < RPT; ++q) { acc[q] = b; xr[q] = Xs + min(r0 + q, R - 1) * ldx; }
         const float* wr = Ws + j * ldw;
+#pragma unroll 8
         for (int i = 0; i < Din; ++i) {
             const float w = wr[i];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) acc[q] = fmaf(xr[q][i], w, acc[q]);
+            for (int q = 0; q < RPT; ++q) acc[q] = fmaf(xr[q][i], w, acc[q]);
         }
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
+        for (int q = 0; q < RPT; ++q) {
             const int r = r0 + q;
             if (r < R) {
                 if (pre_s) pre_s[r * ldy + j] = acc[q];
@@ -74,34 +84,59 @@ __device__ __forceinline__ void linear_fwd(const float* Xs, int ldx, const float
         }
     }
 }
+// Runtime epilogue (activation, residual, dropout site) and ONE out-of-line copy: the kernels call this from a dozen
+// places; inlined and specialised per call site the backward kernel grew to 15 k instructions (~240 KB) and a third of
+// its stall samples were instruction-cache misses (ncu: stall_no_inst).
+// Few rows (one trial per CTA: the cross-validation batch sizes): one row per thread keeps all warps busy instead of 2 of 8.
+struct Epi {
+    int act, res, site, layer, trial0, tok;      // site < 0: no dropout
+};
+__device__ __noinline__ void linear_fwd(const float* Xs, int ldx, const float* Ws, int Din, int Dout, const float* bias,
+                                        float* Ys, int ldy, int R, float* pre_s, const Epi e, const DropCtx& dc) {
+    auto post = [&](int r, int j, float v) {
+        if (e.act == ACT_GELU) v = gelu_f(v);
+        if (e.site >= 0) v *= dc.mask(e.layer, e.site, e.trial0 + r / e.tok, (r % e.tok) * Dout + j);
+        return e.res ? Ys[r * ldy + j] + v : v;
+    };
+    if (((R + 3) >> 2) * Dout >= TR_THREADS) linear_fwd_rpt<ACT_NONE, false, 4>(Xs, ldx, Ws, Din, Dout, bias, Ys, ldy, R, pre_s, post);
+    else if (((R + 1) >> 1) * Dout >= TR_THREADS) linear_fwd_rpt<ACT_NONE, false, 2>(Xs, ldx, Ws, Din, Dout, bias, Ys, ldy, R, pre_s, post);
+    else linear_fwd_rpt<ACT_NONE, false, 1>(Xs, ldx, Ws, Din, Dout, bias, Ys, ldy, R, pre_s, post);
+}
 
 // dX[r][i] (ACC ? += : =) sum_j dY[r][j] W[j][i]
-template <bool ACC>
-__device__ __forceinline__ void linear_dgrad(const float* dYs, int ldy, const float* Ws, int Din, int Dout,
-                                             float* dXs, int ldx, int R) {
+template <bool ACC, int RPT>
+__device__ __forceinline__ void linear_dgrad_rpt(const float* dYs, int ldy, const float* Ws, int Din, int Dout, float* dXs, int ldx,
+                                                 int R) {
     const int ldw = Din + 1;
-    const int RG = (R + 3) >> 2;
+    const int RG = (R + RPT - 1) / RPT;
     for (int idx = threadIdx.x; idx < RG * Din; idx += TR_THREADS) {
-        const int i = idx % Din, r0 = (idx / Din) << 2;
-        float acc[4] = {0.f, 0.f, 0.f, 0.f};
-        const float* yr[4];
+        const int i = idx % Din, r0 = (idx / Din) * RPT;
+        float acc[RPT];
+        const float* yr[RPT];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) yr[q] = dYs + min(r0 + q, R - 1) * ldy;
+        for (int q = 0; q < RPT; ++q) { acc[q] = 0.f; yr[q] = dYs + min(r0 + q, R - 1) * ldy; }
+#pragma unroll 8
         for (int j = 0; j < Dout; ++j) {
             const float w = Ws[j * ldw + i];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) acc[q] = fmaf(yr[q][j], w, acc[q]);
+            for (int q = 0; q < RPT; ++q) acc[q] = fmaf(yr[q][j], w, acc[q]);
         }
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
+        for (int q = 0; q < RPT; ++q) {
             const int r = r0 + q;
             if (r < R) { if (ACC) dXs[r * ldx + i] += acc[q]; else dXs[r * ldx + i] = acc[q]; }
         }
     }
 }
+__device__ __noinline__ void linear_dgrad(const float* dYs, int ldy, const float* Ws, int Din, int Dout, float* dXs, int ldx,
+                                          int R) {
+    if (((R + 3) >> 2) * Din >= TR_THREADS) linear_dgrad_rpt<false, 4>(dYs, ldy, Ws, Din, Dout, dXs, ldx, R);
+    else if (((R + 1) >> 1) * Din >= TR_THREADS) linear_dgrad_rpt<false, 2>(dYs, ldy, Ws, Din, Dout, dXs, ldx, R);
+    else linear_dgrad_rpt<false, 1>(dYs, ldy, Ws, Din, Dout, dXs, ldx, R);
+}
 
 // gW[j][i] += sum_r dY[r][j] X[r][i] ;  gb[j] += sum_r dY[r][j]      (one atomic per element per CTA)
-__device__ __forceinline__ void linear_wgrad(const float* dYs, int ldy, const float* Xs, int ldx, int Din, int Dout,
+__device__ __noinline__ void linear_wgrad(const float* dYs, int ldy, const float* Xs, int ldx, int Din, int Dout,
                                              int R, float* gW, float* gb) {
     for (int idx = threadIdx.x; idx < Dout * Din; idx += TR_THREADS) {
         const int i = idx % Din, j = idx / Din;
@@ -117,8 +152,7 @@ __device__ __forceinline__ void linear_wgrad(const float* dYs, int ldy, const fl
         }
 }
 
-__device__ __forceinline__ void ln_fwd(const float* Xs, float* Ys, const float* __restrict__ w,
-                                       const float* __restrict__ b, int R, int D, float* stat) {
+__device__ __noinline__ void ln_fwd(const float* Xs, float* Ys, const float* w, const float* b, int R, int D, float* stat) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int r = warp; r < R; r += TR_WARPS) {
         float s = 0.f;
@@ -127,25 +161,25 @@ __device__ __forceinline__ void ln_fwd(const float* Xs, float* Ys, const float* 
         float v = 0.f;
         for (int i = lane; i < D; i += 32) { const float d = Xs[r * D + i] - mean; v = fmaf(d, d, v); }
         const float rstd = 1.0f / sqrtf(warp_sum(v) / (float)D + LN_EPS);
-        for (int i = lane; i < D; i += 32) Ys[r * D + i] = (Xs[r * D + i] - mean) * rstd * __ldg(w + i) + __ldg(b + i);
+        for (int i = lane; i < D; i += 32) Ys[r * D + i] = (Xs[r * D + i] - mean) * rstd * w[i] + b[i];
         if (stat && lane == 0) { stat[2 * r] = mean; stat[2 * r + 1] = rstd; }
     }
 }
 
 // dXout[r][i] += rstd (g - mean(g) - xhat mean(g xhat)), g = dY w ;  gw += sum_r dY xhat ; gb += sum_r dY
-__device__ __forceinline__ void ln_bwd(const float* dYs, const float* Xs, const float* stat,
-                                       const float* __restrict__ w, float* dXout, int R, int D, float* gw, float* gb) {
+__device__ __noinline__ void ln_bwd(const float* dYs, const float* Xs, const float* stat, const float* w, float* dXout, int R,
+                                       int D, float* gw, float* gb) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int r = warp; r < R; r += TR_WARPS) {
         const float mean = stat[2 * r], rstd = stat[2 * r + 1];
         float a = 0.f, c = 0.f;
         for (int i = lane; i < D; i += 32) {
-            const float g = dYs[r * D + i] * __ldg(w + i), xh = (Xs[r * D + i] - mean) * rstd;
+            const float g = dYs[r * D + i] * w[i], xh = (Xs[r * D + i] - mean) * rstd;
             a += g; c = fmaf(g, xh, c);
         }
         a = warp_sum(a) / (float)D; c = warp_sum(c) / (float)D;
         for (int i = lane; i < D; i += 32) {
-            const float g = dYs[r * D + i] * __ldg(w + i), xh = (Xs[r * D + i] - mean) * rstd;
+            const float g = dYs[r * D + i] * w[i], xh = (Xs[r * D + i] - mean) * rstd;
             dXout[r * D + i] += rstd * (g - a - xh * c);
         }
     }
@@ -162,7 +196,7 @@ __device__ __forceinline__ void ln_bwd(const float* dYs, const float* Xs, const 
 }
 
 // softmax(q k^T / sqrt(hd)) per (trial, head, query) thread; P kept for the backward; O = dropout(P) v
-__device__ __forceinline__ void attention_fwd(const float* QKV, float* P, float* O, int G, int tok, int D, int H,
+__device__ __noinline__ void attention_fwd(const float* QKV, float* P, float* O, int G, int tok, int D, int H,
                                               const DropCtx& dc, int layer, int trial0) {
     const int hd = D / H;
     const float scale = 1.0f / sqrtf((float)hd);
@@ -183,11 +217,26 @@ __device__ __forceinline__ void attention_fwd(const float* QKV, float* P, float*
         const float inv = 1.0f / sum;
         for (int j = 0; j < tok; ++j) prow[j] *= inv;
         const float* vbase = kbase + D;
-        for (int d = 0; d < hd; ++d) {
-            float acc = 0.f;
-            for (int j = 0; j < tok; ++j)
-                acc = fmaf(prow[j] * dc.mask(layer, SITE_ATTN, trial0 + g, (h * tok + i) * tok + j), vbase[j * 3 * D + d], acc);
-            O[(g * tok + i) * D + h * hd + d] = acc;
+        if (hd <= 8) {                                  // one mask draw per key instead of one per (key, channel)
+            float acc[8];
+#pragma unroll
+            for (int d = 0; d < 8; ++d) acc[d] = 0.f;
+            for (int j = 0; j < tok; ++j) {
+                const float pm = prow[j] * dc.mask(layer, SITE_ATTN, trial0 + g, (h * tok + i) * tok + j);
+#pragma unroll
+                for (int d = 0; d < 8; ++d)
+                    if (d < hd) acc[d] = fmaf(pm, vbase[j * 3 * D + d], acc[d]);
+            }
+#pragma unroll
+            for (int d = 0; d < 8; ++d)
+                if (d < hd) O[(g * tok + i) * D + h * hd + d] = acc[d];
+        } else {
+            for (int d = 0; d < hd; ++d) {
+                float acc = 0.f;
+                for (int j = 0; j < tok; ++j)
+                    acc = fmaf(prow[j] * dc.mask(layer, SITE_ATTN, trial0 + g, (h * tok + i) * tok + j), vbase[j * 3 * D + d], acc);
+                O[(g * tok + i) * D + h * hd + d] = acc;
+            }
         }
     }
 }
@@ -195,26 +244,47 @@ __device__ __forceinline__ void attention_fwd(const float* QKV, float* P, float*
 // one AttentionBlock forward over the CTA's rows.  Buffers: X (in/out), Hn, QKV, P, O, U (hidden), Upre (or null).
 struct BlockBufs { float *X, *Hn, *QKV, *P, *O, *U, *Upre, *stat1, *stat2, *Xmid, *Hn2; };
 
+// the block's vectors (LayerNorm affine, biases) ride along in shared memory: every phase used to open with a dependent global load
+struct BlockVec { const float *ln1_w, *ln1_b, *qkv_b, *out_b, *ln2_w, *ln2_b, *ff1_b, *ff2_b; };
+
+__device__ __forceinline__ const float* stage_v(float*& dst, const float* __restrict__ src, int n) {
+    float* d0 = dst;
+    for (int i = threadIdx.x; i < n; i += TR_THREADS) {
+        const unsigned d = (unsigned)__cvta_generic_to_shared(d0 + i);
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(src + i) : "memory");
+    }
+    dst += n;
+    return d0;
+}
+
 __device__ __forceinline__ void stage_block(const fastb200_model& m, const float* params, int l, float* Ws,
-                                            float*& Wqkv, float*& Wo, float*& W1, float*& W2) {
+                                            float*& Wqkv, float*& Wo, float*& W1, float*& W2, BlockVec& bv) {
     const int D = m.dim_token, Hd = m.dim_hidden;
     Wqkv = Ws; Wo = Wqkv + 3 * D * (D + 1); W1 = Wo + D * (D + 1); W2 = W1 + Hd * (D + 1);
     stage_w(Wqkv, params + m.off_qkv_w[l], 3 * D, D);
     stage_w(Wo, params + m.off_out_w[l], D, D);
     stage_w(W1, params + m.off_ff1_w[l], Hd, D);
     stage_w(W2, params + m.off_ff2_w[l], D, Hd);
+    float* v = W2 + D * (Hd + 1);
+    bv.ln1_w = stage_v(v, params + m.off_ln1_w[l], D);
+    bv.ln1_b = stage_v(v, params + m.off_ln1_b[l], D);
+    bv.qkv_b = stage_v(v, params + m.off_qkv_b[l], 3 * D);
+    bv.out_b = stage_v(v, params + m.off_out_b[l], D);
+    bv.ln2_w = stage_v(v, params + m.off_ln2_w[l], D);
+    bv.ln2_b = stage_v(v, params + m.off_ln2_b[l], D);
+    bv.ff1_b = stage_v(v, params + m.off_ff1_b[l], Hd);
+    bv.ff2_b = stage_v(v, params + m.off_ff2_b[l], D);
 }
 
 // KEEP = true (backward recompute): keeps Xmid, Hn2, Upre, LN statistics, and leaves X untouched.
 template <bool KEEP>
 __device__ __forceinline__ void block_fwd(const fastb200_model& m, const float* params, int l, const BlockBufs& bb,
-                                          const float* Wqkv, const float* Wo, const float* W1, const float* W2, int G,
-                                          int tok, const DropCtx& dc, int trial0) {
+                                          const float* Wqkv, const float* Wo, const float* W1, const float* W2,
+                                          const BlockVec& bv, int G, int tok, const DropCtx& dc, int trial0) {
     const int D = m.dim_token, Hd = m.dim_hidden, R = G * tok;
-    auto ident = [](int, int, float v) { return v; };
-    ln_fwd(bb.X, bb.Hn, params + m.off_ln1_w[l], params + m.off_ln1_b[l], R, D, bb.stat1);
+    ln_fwd(bb.X, bb.Hn, bv.ln1_w, bv.ln1_b, R, D, bb.stat1);
     __syncthreads();
-    linear_fwd<ACT_NONE, false>(bb.Hn, D, Wqkv, D, 3 * D, params + m.off_qkv_b[l], bb.QKV, 3 * D, R, nullptr, ident);
+    linear_fwd(bb.Hn, D, Wqkv, D, 3 * D, bv.qkv_b, bb.QKV, 3 * D, R, nullptr, Epi{ACT_NONE, 0, -1, l, trial0, tok}, dc);
     __syncthreads();
     attention_fwd(bb.QKV, bb.P, bb.O, G, tok, D, m.n_heads, dc, l, trial0);
     __syncthreads();
@@ -223,17 +293,15 @@ __device__ __forceinline__ void block_fwd(const fastb200_model& m, const float* 
         for (int i = threadIdx.x; i < R * D; i += TR_THREADS) bb.Xmid[i] = bb.X[i];
         __syncthreads();
     }
-    linear_fwd<ACT_NONE, true>(bb.O, D, Wo, D, D, params + m.off_out_b[l], xmid, D, R, nullptr, ident);
+    linear_fwd(bb.O, D, Wo, D, D, bv.out_b, xmid, D, R, nullptr, Epi{ACT_NONE, 1, -1, l, trial0, tok}, dc);
     __syncthreads();
     float* hn2 = KEEP ? bb.Hn2 : bb.Hn;
-    ln_fwd(xmid, hn2, params + m.off_ln2_w[l], params + m.off_ln2_b[l], R, D, bb.stat2);
+    ln_fwd(xmid, hn2, bv.ln2_w, bv.ln2_b, R, D, bb.stat2);
     __syncthreads();
-    auto drop_hid = [&](int r, int j, float v) { return v * dc.mask(l, SITE_FFN_HID, trial0 + r / tok, (r % tok) * Hd + j); };
-    linear_fwd<ACT_GELU, false>(hn2, D, W1, D, Hd, params + m.off_ff1_b[l], bb.U, Hd, R, KEEP ? bb.Upre : nullptr, drop_hid);
+    linear_fwd(hn2, D, W1, D, Hd, bv.ff1_b, bb.U, Hd, R, KEEP ? bb.Upre : nullptr, Epi{ACT_GELU, 0, SITE_FFN_HID, l, trial0, tok}, dc);
     __syncthreads();
     if (!KEEP) {
-        auto drop_out = [&](int r, int j, float v) { return v * dc.mask(l, SITE_FFN_OUT, trial0 + r / tok, (r % tok) * D + j); };
-        linear_fwd<ACT_NONE, true>(bb.U, Hd, W2, Hd, D, params + m.off_ff2_b[l], bb.X, D, R, nullptr, drop_out);
+        linear_fwd(bb.U, Hd, W2, Hd, D, bv.ff2_b, bb.X, D, R, nullptr, Epi{ACT_NONE, 1, SITE_FFN_OUT, l, trial0, tok}, dc);
         __syncthreads();
     }
 }
@@ -256,7 +324,7 @@ struct TrArgs {
 
 __device__ __forceinline__ int tr_ws_floats(const fastb200_model& m) {
     const int D = m.dim_token, Hd = m.dim_hidden, ZF = m.n_zones * m.dim_cnn;
-    const int blk = 3 * D * (D + 1) + D * (D + 1) + Hd * (D + 1) + D * (Hd + 1);
+    const int blk = 3 * D * (D + 1) + D * (D + 1) + Hd * (D + 1) + D * (Hd + 1) + 9 * D + Hd;     // weights + vectors
     const int inp = D * (ZF + 1);
     return round_up(blk > inp ? blk : inp, 4);
 }
@@ -267,9 +335,10 @@ __device__ __forceinline__ void input_layer_fwd(const fastb200_model& m, const T
     const int D = m.dim_token, ZF = m.n_zones * m.dim_cnn, Rin = G * a.n_win;
     stage_w(Ws, a.params + m.off_in_w, D, ZF);
     for (int i = threadIdx.x; i < Rin * ZF; i += TR_THREADS) Fs[i] = __ldg(a.feat + (size_t)trial0 * a.n_win * ZF + i);
+    stage_wait();
     __syncthreads();
-    auto ident = [](int, int, float v) { return v; };
-    linear_fwd<ACT_GELU, false>(Fs, ZF, Ws, ZF, D, a.params + m.off_in_b, Ts, D, Rin, pre, ident);
+    DropCtx none{};
+    linear_fwd(Fs, ZF, Ws, ZF, D, a.params + m.off_in_b, Ts, D, Rin, pre, Epi{ACT_GELU, 0, -1, 0, trial0, 1}, none);
     __syncthreads();
 }
 
@@ -317,14 +386,16 @@ __global__ void __launch_bounds__(TR_THREADS) transformer_fwd_kernel(const __gri
     BlockBufs bb{X, Hn, QKV, P, O, U, nullptr, nullptr, nullptr, nullptr, nullptr};
     for (int l = 0; l < m.n_layers; ++l) {
         float *Wqkv, *Wo, *W1, *W2;
-        stage_block(m, a.params, l, Ws, Wqkv, Wo, W1, W2);
+        BlockVec bv;
+        stage_block(m, a.params, l, Ws, Wqkv, Wo, W1, W2, bv);
         if (a.saved)
             for (int idx = threadIdx.x; idx < R * D; idx += TR_THREADS) {
                 const int g = idx / (tok * D), rem = idx - g * tok * D;
                 a.saved[((size_t)(trial0 + g) * (m.n_layers + 1) + l) * tok * D + rem] = X[idx];
             }
+        stage_wait();
         __syncthreads();
-        block_fwd<false>(m, a.params, l, bb, Wqkv, Wo, W1, W2, G, tok, dc, trial0);
+        block_fwd<false>(m, a.params, l, bb, Wqkv, Wo, W1, W2, bv, G, tok, dc, trial0);
     }
     if (a.saved)
         for (int idx = threadIdx.x; idx < R * D; idx += TR_THREADS) {
@@ -408,13 +479,15 @@ __global__ void __launch_bounds__(TR_THREADS) transformer_bwd_kernel(const __gri
         BlockBufs bb{X, Hn, QKV, P, O, U, Upre, stat1, stat2, Xmid, Hn2};
         for (int l = L - 1; l >= 0; --l) {
             float *Wqkv, *Wo, *W1, *W2;
-            stage_block(m, a.params, l, Ws, Wqkv, Wo, W1, W2);
+            BlockVec bv;
+            stage_block(m, a.params, l, Ws, Wqkv, Wo, W1, W2, bv);
             for (int idx = threadIdx.x; idx < R * D; idx += TR_THREADS) {
                 const int gg = idx / (tok * D), rem = idx - gg * tok * D;
                 X[idx] = __ldg(a.saved + ((size_t)(trial0 + gg) * (L + 1) + l) * tok * D + rem);
             }
+            stage_wait();
             __syncthreads();
-            block_fwd<true>(m, a.params, l, bb, Wqkv, Wo, W1, W2, G, tok, dc, trial0);   // recompute, X intact
+            block_fwd<true>(m, a.params, l, bb, Wqkv, Wo, W1, W2, bv, G, tok, dc, trial0);   // recompute, X intact
 
             // ---- FFN: X_out = Xmid + drop(W2 U + b2),  U = drop(gelu(Upre)),  Upre = W1 Hn2 + b1
             for (int idx = threadIdx.x; idx < R * D; idx += TR_THREADS) {
@@ -423,7 +496,7 @@ __global__ void __launch_bounds__(TR_THREADS) transformer_bwd_kernel(const __gri
             }
             __syncthreads();
             linear_wgrad(dT, D, U, Hd, Hd, D, R, g + m.off_ff2_w[l], g + m.off_ff2_b[l]);
-            linear_dgrad<false>(dT, D, W2, Hd, D, dBig, Hd, R);
+            linear_dgrad(dT, D, W2, Hd, D, dBig, Hd, R);
             __syncthreads();
             for (int idx = threadIdx.x; idx < R * Hd; idx += TR_THREADS) {
                 const int j = idx % Hd, r = idx / Hd;
@@ -431,13 +504,13 @@ __global__ void __launch_bounds__(TR_THREADS) transformer_bwd_kernel(const __gri
             }
             __syncthreads();
             linear_wgrad(dBig, Hd, Hn2, D, D, Hd, R, g + m.off_ff1_w[l], g + m.off_ff1_b[l]);
-            linear_dgrad<false>(dBig, Hd, W1, D, Hd, dT, D, R);          // dT <- dHn2
+            linear_dgrad(dBig, Hd, W1, D, Hd, dT, D, R);          // dT <- dHn2
             __syncthreads();
-            ln_bwd(dT, Xmid, stat2, a.params + m.off_ln2_w[l], dX, R, D, g + m.off_ln2_w[l], g + m.off_ln2_b[l]);
+            ln_bwd(dT, Xmid, stat2, bv.ln2_w, dX, R, D, g + m.off_ln2_w[l], g + m.off_ln2_b[l]);
             __syncthreads();                                             // dX now holds dL/dXmid
             // ---- attention: Xmid = X + Wo O + bo
             linear_wgrad(dX, D, O, D, D, D, R, g + m.off_out_w[l], g + m.off_out_b[l]);
-            linear_dgrad<false>(dX, D, Wo, D, D, dT, D, R);              // dT <- dO
+            linear_dgrad(dX, D, Wo, D, D, dT, D, R);              // dT <- dO
             __syncthreads();
             const float scale = 1.0f / sqrtf((float)hd);
             // dS[i][j] = P (dP - sum_j dP P), dP = mask * (dO_i . v_j)
@@ -477,9 +550,9 @@ __global__ void __launch_bounds__(TR_THREADS) transformer_bwd_kernel(const __gri
             }
             __syncthreads();
             linear_wgrad(dBig, 3 * D, Hn, D, D, 3 * D, R, g + m.off_qkv_w[l], g + m.off_qkv_b[l]);
-            linear_dgrad<false>(dBig, 3 * D, Wqkv, D, 3 * D, dT, D, R);   // dT <- dHn
+            linear_dgrad(dBig, 3 * D, Wqkv, D, 3 * D, dT, D, R);   // dT <- dHn
             __syncthreads();
-            ln_bwd(dT, X, stat1, a.params + m.off_ln1_w[l], dX, R, D, g + m.off_ln1_w[l], g + m.off_ln1_b[l]);
+            ln_bwd(dT, X, stat1, bv.ln1_w, dX, R, D, g + m.off_ln1_w[l], g + m.off_ln1_b[l]);
             __syncthreads();                                             // dX now holds dL/dX_l
         }
         // ---- X_0 = cat(cls, T) + pos
@@ -528,7 +601,7 @@ __global__ void __launch_bounds__(TR_THREADS) transformer_bwd_kernel(const __gri
     __syncthreads();
     linear_wgrad(dT, D, Fs, ZF, ZF, D, Rin, g + m.off_in_w, g + m.off_in_b);
     __syncthreads();                                                     // every thread is done reading Fs
-    if (a.dfeat) linear_dgrad<false>(dT, D, Ws, ZF, D, Fs, ZF, Rin);     // Fs <- dfeat
+    if (a.dfeat) linear_dgrad(dT, D, Ws, ZF, D, Fs, ZF, Rin);     // Fs <- dfeat
     __syncthreads();
     if (a.dfeat)
         for (int i = threadIdx.x; i < Rin * ZF; i += TR_THREADS) a.dfeat[(size_t)trial0 * n_win * ZF + i] = Fs[i];
@@ -539,7 +612,7 @@ __global__ void __launch_bounds__(TR_THREADS) transformer_bwd_kernel(const __gri
 // ---------------------------------------------------------------------------------------------------------
 static int host_ws_floats(const fastb200_model& m) {
     const int D = m.dim_token, Hd = m.dim_hidden, ZF = m.n_zones * m.dim_cnn;
-    const int blk = 3 * D * (D + 1) + D * (D + 1) + Hd * (D + 1) + D * (Hd + 1);
+    const int blk = 3 * D * (D + 1) + D * (D + 1) + Hd * (D + 1) + D * (Hd + 1) + 9 * D + Hd;     // weights + vectors
     const int inp = D * (ZF + 1);
     return round_up(blk > inp ? blk : inp, 4);
 }
@@ -571,7 +644,8 @@ static int validate_tr(const fastb200_model* m, int B, int n_win, int mode, floa
 template <typename SizeFn>
 static int pick_group(const fastb200_model& m, int B, int tok, int n_win, SizeFn size_fn, size_t budget) {
     int G = 1;
-    const int want = ceil_div(B, 2 * NUM_SMS);
+    int want = ceil_div(B, 2 * NUM_SMS);
+    if (const char* e = getenv("FASTB200_TR_GROUP")) want = atoi(e) > 0 ? atoi(e) : want;     // tuning probe
     while (G < want && G < 16 && size_fn(m, G + 1, tok, n_win) * sizeof(float) <= budget) ++G;
     return G;
 }

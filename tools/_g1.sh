@@ -1,2 +1,2 @@
-python -m pytest tests -m gpu -x -q -k "filter or resample or sosfilt" 2>&1 | tail -3
-python bench.py --workload preprocess --no-extras 2>&1 | tail -1 | python -c "import json,sys;d=json.loads(sys.stdin.read());print(d['value'],d['roofline']['ms_per_launch'],d['roofline']['two_kernel_chain_ms'])"
+ncu --set full --clock-control none --import-source on -k regex:'transformer_(fwd|bwd)' -s 8 -c 2 -o gpurun_out/r01_tr_b64 --force-overwrite python bench.py --workload train --batch 64 --no-extras --steps 2 --warmup 3 > gpurun_out/ncu_tr.log 2>&1
+ls -la gpurun_out/r01_tr_b64.ncu-rep
