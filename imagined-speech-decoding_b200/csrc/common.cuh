@@ -118,6 +118,22 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     __trap();
 }
 
+// Cooperative copy of a [n_rows][row_len] global array into shared memory with pitch row_len + 1 (all loads in flight at
+// once, coalesced; the odd pitch keeps "one row per lane" readers conflict-free).  Caller runs stage_rows_wait() and __syncthreads().
+__device__ __forceinline__ void stage_rows_pitched(float* dst, const float* __restrict__ src, int n_rows, int row_len) {
+    int r = threadIdx.x / row_len, c = threadIdx.x - r * row_len;
+    const int dr = blockDim.x / row_len, dcol = blockDim.x - dr * row_len;
+    for (int i = threadIdx.x; i < n_rows * row_len; i += blockDim.x) {
+        // cp.async, not load + store: through registers every element waits out its own L2 latency (the compiler cannot
+        // hoist the loads over the shared-memory stores)
+        const unsigned d = (unsigned)__cvta_generic_to_shared(dst + r * (row_len + 1) + c);
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(src + i) : "memory");
+        r += dr; c += dcol;
+        if (c >= row_len) { c -= row_len; ++r; }
+    }
+}
+__device__ __forceinline__ void stage_rows_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 // counter-based uniform in [0,1): (seed, offset, index) -> float.  Used for dropout masks that must be
 // reproduced bit-for-bit by the backward kernel.  (splitmix64-style finaliser; not torch's Philox stream.)
 __device__ __forceinline__ float uniform01(uint64_t seed, uint64_t offset, uint64_t idx) {

@@ -41,7 +41,11 @@ __device__ __forceinline__ int pz_w3(int Cz, int F) { return pz_beff(Cz, F) + ro
 // ---------------------------------------------------------------------------------------------------------
 // weight packing
 // ---------------------------------------------------------------------------------------------------------
-__global__ void head_pack_kernel(fastb200_model m, const float* __restrict__ params, float* __restrict__ packed) {
+// `staged`: cnn2.weight of the zone is first copied to shared memory (row f at pitch F*Cz + 1).  The collapse loops read it
+// with one f per lane, i.e. at a stride of F*Cz floats: from global memory that is one cache line per lane and a chain of
+// dependent-latency loads (these tiny kernels were 15-20 us each, 10 % of a batch-64 training step).
+__global__ void head_pack_kernel(fastb200_model m, const float* __restrict__ params, float* __restrict__ packed, int staged) {
+    extern __shared__ __align__(16) float pk_s[];
     const int z = blockIdx.x;
     const int F = m.dim_cnn, Cz = m.zone_size[z];
     const PackedZone p = packed_zone(m, z);
@@ -50,10 +54,19 @@ __global__ void head_pack_kernel(fastb200_model m, const float* __restrict__ par
     const float* w2 = params + m.off_cnn2_w[z];
     const float* w3 = params + m.off_cnn3_w[z];
     const float* w4 = params + m.off_cnn4_w[z];
+    int fp = F * Cz;                                              // pitch of one f-slab of w2
+    if (staged) {
+        stage_rows_pitched(pk_s, w2, F, F * Cz);
+        stage_rows_wait();
+        __syncthreads();
+        w2 = pk_s;
+        fp = F * Cz + 1;
+    }
     for (int i = threadIdx.x + blockDim.x * blockIdx.y; i < Cz * TAPS * F; i += blockDim.x * gridDim.y) {
         const int f = i % F, k = (i / F) % TAPS, c = i / (F * TAPS);
         float s = 0.f;
-        for (int g = 0; g < F; ++g) s = fmaf(w2[(f * F + g) * Cz + c], w1[g * TAPS + k], s);
+#pragma unroll 8
+        for (int g = 0; g < F; ++g) s = fmaf(w2[f * fp + g * Cz + c], __ldg(w1 + g * TAPS + k), s);
         packed[p.weff + i] = s;
     }
     // beff[f] = sum_g b1[g] * sum_c w2[f,g,c]: one warp per f, lane = g (a serial 32 x Cz chain of dependent loads per thread
@@ -64,7 +77,7 @@ __global__ void head_pack_kernel(fastb200_model m, const float* __restrict__ par
             float v = 0.f;
             if (lane < F) {
                 float r = 0.f;
-                for (int c = 0; c < Cz; ++c) r += w2[(f * F + lane) * Cz + c];
+                for (int c = 0; c < Cz; ++c) r += w2[f * fp + lane * Cz + c];
                 v = r * b1[lane];
             }
             v = warp_sum(v);
@@ -84,7 +97,8 @@ __global__ void head_pack_kernel(fastb200_model m, const float* __restrict__ par
 
 // gradient chain rule: packed-layout grads -> parameter-layout grads
 __global__ void head_unpack_grad_kernel(fastb200_model m, const float* __restrict__ params,
-                                        const float* __restrict__ gp, float* __restrict__ grads) {
+                                        const float* __restrict__ gp, float* __restrict__ grads, int staged) {
+    extern __shared__ __align__(16) float pk_s[];
     const int z = blockIdx.x;
     const int F = m.dim_cnn, Cz = m.zone_size[z];
     const PackedZone p = packed_zone(m, z);
@@ -93,6 +107,16 @@ __global__ void head_unpack_grad_kernel(fastb200_model m, const float* __restric
     const float* w2 = params + m.off_cnn2_w[z];
     const float* gweff = gp + p.weff;   // [c][k][f]
     const float* gbeff = gp + p.beff;   // [f]
+    int fp = F * Cz, cp = TAPS * F;                               // pitches of w2's f-slabs and of gweff's c-slabs
+    if (staged) {                                                 // see head_pack_kernel
+        float* gs = pk_s + F * (F * Cz + 1);
+        stage_rows_pitched(pk_s, w2, F, F * Cz);
+        stage_rows_pitched(gs, gweff, Cz, TAPS * F);
+        stage_rows_wait();
+        __syncthreads();
+        w2 = pk_s; fp = F * Cz + 1;
+        gweff = gs; cp = TAPS * F + 1;
+    }
     // d cnn1.weight[g,k] = sum_{f,c} gweff[c,k,f] * w2[f,g,c]
     // (one warp per output, lane = f: the serial F x Cz chains of dependent loads dominated this kernel)
     const int lane = threadIdx.x & 31, wg = (threadIdx.x >> 5) + (blockDim.x >> 5) * blockIdx.y, nw = (blockDim.x >> 5) * gridDim.y;
@@ -100,7 +124,7 @@ __global__ void head_unpack_grad_kernel(fastb200_model m, const float* __restric
         const int g = i / TAPS, k = i % TAPS;
         float s = 0.f;
         if (lane < F)
-            for (int c = 0; c < Cz; ++c) s = fmaf(gweff[(c * TAPS + k) * F + lane], w2[(lane * F + g) * Cz + c], s);
+            for (int c = 0; c < Cz; ++c) s = fmaf(gweff[c * cp + k * F + lane], w2[lane * fp + g * Cz + c], s);
         s = warp_sum(s);
         if (lane == 0) grads[m.off_cnn1_w[z] + i] = s;
     }
@@ -109,7 +133,7 @@ __global__ void head_unpack_grad_kernel(fastb200_model m, const float* __restric
         float s = 0.f;
         if (lane < F) {
             float r = 0.f;
-            for (int c = 0; c < Cz; ++c) r += w2[(lane * F + g) * Cz + c];
+            for (int c = 0; c < Cz; ++c) r += w2[lane * fp + g * Cz + c];
             s = gbeff[lane] * r;
         }
         s = warp_sum(s);
@@ -119,7 +143,8 @@ __global__ void head_unpack_grad_kernel(fastb200_model m, const float* __restric
     for (int i = threadIdx.x + blockDim.x * blockIdx.y; i < F * F * Cz; i += blockDim.x * gridDim.y) {
         const int c = i % Cz, g = (i / Cz) % F, f = i / (Cz * F);
         float s = gbeff[f] * b1[g];
-        for (int k = 0; k < TAPS; ++k) s = fmaf(gweff[(c * TAPS + k) * F + f], w1[g * TAPS + k], s);
+#pragma unroll
+        for (int k = 0; k < TAPS; ++k) s = fmaf(gweff[c * cp + k * F + f], __ldg(w1 + g * TAPS + k), s);
         grads[m.off_cnn2_w[z] + i] = s;
     }
     // cnn3 / cnn4: packed [ci][k][co] -> (co, ci, 1, k)
@@ -737,14 +762,30 @@ extern "C" int64_t fastb200_head_saved_floats(const fastb200_model* m, int B, in
 
 extern "C" int fastb200_head_pack(const fastb200_model* m, const float* params, float* packed, void* stream) {
     if (int r = validate_model(m)) return r;
-    head_pack_kernel<<<dim3(m->n_zones, 8), 256, 0, as_stream(stream)>>>(*m, params, packed);
+    int czmax = 0;
+    for (int z = 0; z < m->n_zones; ++z) czmax = czmax > m->zone_size[z] ? czmax : m->zone_size[z];
+    size_t smem = (size_t)m->dim_cnn * (m->dim_cnn * czmax + 1) * sizeof(float);
+    int staged = smem <= 200 * 1024;
+    if (staged && smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(head_pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return fail((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    }
+    head_pack_kernel<<<dim3(m->n_zones, 8), 256, staged ? smem : 0, as_stream(stream)>>>(*m, params, packed, staged);
     return check_launch("head_pack");
 }
 
 extern "C" int fastb200_head_unpack_grad(const fastb200_model* m, const float* params, const float* gpacked,
                                          float* grads, void* stream) {
     if (int r = validate_model(m)) return r;
-    head_unpack_grad_kernel<<<dim3(m->n_zones, 8), 256, 0, as_stream(stream)>>>(*m, params, gpacked, grads);
+    int czmax = 0;
+    for (int z = 0; z < m->n_zones; ++z) czmax = czmax > m->zone_size[z] ? czmax : m->zone_size[z];
+    size_t smem = ((size_t)m->dim_cnn * (m->dim_cnn * czmax + 1) + (size_t)czmax * (TAPS * m->dim_cnn + 1)) * sizeof(float);
+    int staged = smem <= 200 * 1024;
+    if (staged && smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(head_unpack_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return fail((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    }
+    head_unpack_grad_kernel<<<dim3(m->n_zones, 8), 256, staged ? smem : 0, as_stream(stream)>>>(*m, params, gpacked, grads, staged);
     return check_launch("head_unpack_grad");
 }
 

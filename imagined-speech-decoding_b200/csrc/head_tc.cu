@@ -63,6 +63,7 @@ __device__ __forceinline__ void store_split(uint16_t* blk, int NT, int chunk, in
 }
 
 __global__ void head_pack_tc_kernel(fastb200_model m, const float* __restrict__ params, uint8_t* __restrict__ packed, int NT) {
+    extern __shared__ __align__(16) float pk_s[];                // cnn2.weight of the zone, f-slabs at pitch F*Cz + 1 (see head_pack_kernel)
     const int z = blockIdx.x;
     const int Cz = m.zone_size[z];
     const int Czp = Cz <= 8 ? 8 : 16;
@@ -76,13 +77,20 @@ __global__ void head_pack_tc_kernel(fastb200_model m, const float* __restrict__ 
     const float* w2 = params + m.off_cnn2_w[z];
     const float* w3 = params + m.off_cnn3_w[z];
     const float* w4 = params + m.off_cnn4_w[z];
+    stage_rows_pitched(pk_s, w2, F, F * Cz);
+    stage_rows_wait();
+    __syncthreads();
+    w2 = pk_s;
+    const int fp = F * Cz + 1;
     // collapsed cnn1 o cnn2 (same summation order as head_pack_kernel in head.cu)
     for (int i = threadIdx.x + blockDim.x * blockIdx.y; i < EMB_CHUNKS * 8 * F; i += blockDim.x * gridDim.y) {
         const int f = i % F, kk = i / F;
         const int k = kk / Czp, c = kk % Czp;
         float s = 0.f;
-        if (k < TAPS && c < Cz)
-            for (int g = 0; g < F; ++g) s = fmaf(w2[(f * F + g) * Cz + c], w1[g * TAPS + k], s);
+        if (k < TAPS && c < Cz) {
+#pragma unroll 8
+            for (int g = 0; g < F; ++g) s = fmaf(w2[f * fp + g * Cz + c], __ldg(w1 + g * TAPS + k), s);
+        }
         store_split(emb, NT, kk / 8, f, kk % 8, s);
     }
     {   // beff[f] = sum_g b1[g] * sum_c w2[f,g,c]: one warp per f, lane = g (as head_pack_kernel)
@@ -90,7 +98,7 @@ __global__ void head_pack_tc_kernel(fastb200_model m, const float* __restrict__ 
         for (int f = wg; f < F; f += nw) {
             float r = 0.f;
             if (lane < F) {
-                for (int c = 0; c < Cz; ++c) r += w2[(f * F + lane) * Cz + c];
+                for (int c = 0; c < Cz; ++c) r += w2[f * fp + lane * Cz + c];
                 r *= b1[lane];
             }
             const float v = warp_sum(r);
@@ -538,7 +546,11 @@ extern "C" int64_t fastb200_head_packed_tc_bytes(const fastb200_model* m, int n_
 
 extern "C" int fastb200_head_pack_tc(const fastb200_model* m, const float* params, void* packed, int n_terms, void* stream) {
     if (int r = tc_supported(m, n_terms)) return r;
-    tc::head_pack_tc_kernel<<<dim3(m->n_zones, 8), 256, 0, as_stream(stream)>>>(*m, params, static_cast<uint8_t*>(packed), n_terms);
+    // the tensor-core path requires F = 32 and zones of <= 16 electrodes: the staged cnn2.weight is at most 65.7 KB
+    const size_t smem = (size_t)tc::F * (tc::F * 16 + 1) * sizeof(float);
+    cudaError_t e = cudaFuncSetAttribute(tc::head_pack_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return fb::fail((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    tc::head_pack_tc_kernel<<<dim3(m->n_zones, 8), 256, smem, as_stream(stream)>>>(*m, params, static_cast<uint8_t*>(packed), n_terms);
     return check_launch("head_pack_tc");
 }
 
