@@ -628,7 +628,9 @@ def run_cv(args, rank, world, local_rank):
     import tempfile
     dev, dist = _dist_setup(world, local_rank)
     from fast.data import SUBJECTS
+    from fast.models import fast as FM
     from fast.train import cv as CV
+    FM.set_head_precision(args.head_precision)
     cfg = prod_cfg()
     subjects = SUBJECTS[:args.subjects]
     jobs = CV.cv_jobs(subjects, 5)
@@ -674,7 +676,7 @@ def run_cv(args, rank, world, local_rank):
     steps = len(jobs) * args.epochs * 5
     line = {"metric": "15-subject x 5-fold CV wall-clock", "value": dev_s, "unit": "s", "n_gpus": world, "steps": steps, "warmup": 1,
             "ms_per_step": 1e3 * dev_s / max(1, len(mine) * args.epochs * 5), "higher_is_better": False, "scaling": "strong",
-            "vs_baseline": None, "dtype": "f32 train / bf16x3 eval", "data": "synthetic", "clocks": clocks.summary(),
+            "vs_baseline": None, "dtype": _train_dtype(FM), "data": "synthetic", "clocks": clocks.summary(),
             "config": {"workload": "BASELINE configs[3]: per-subject 5-fold CV of FAST, batch 64", "jobs": len(jobs), "jobs_this_rank": len(mine),
                        "epochs": args.epochs, "subjects": len(subjects), "trials_per_subject": 350, "batch": args.cv_batch,
                        "parallelism": f"subject x fold jobs sharded x{world}, no collective", "host_wall_s": wall,

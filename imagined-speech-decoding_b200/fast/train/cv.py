@@ -188,9 +188,14 @@ def train_fold(config, x, y, train_idx, val_idx, max_epochs=200, batch_size=64, 
                 graph = torch.cuda.CUDAGraph()
                 side = torch.cuda.Stream(dev)
                 side.wait_stream(torch.cuda.current_stream(dev))
+                # capture_begin / capture_end directly: the torch.cuda.graph context also runs gc.collect() and empties the
+                # device and pinned-host caches on entry, tens of ms per job that 75 jobs pay 75 times
                 with torch.cuda.stream(side):
-                    with torch.cuda.graph(graph, stream=side):
+                    graph.capture_begin()
+                    try:
                         epoch_body()
+                    finally:
+                        graph.capture_end()
                 torch.cuda.current_stream(dev).wait_stream(side)
             graph.replay()
         ft.steps_done += n_it
@@ -198,7 +203,16 @@ def train_fold(config, x, y, train_idx, val_idx, max_epochs=200, batch_size=64, 
     with torch.no_grad():
         final = ft.flat.clone()
         ft.flat.copy_(best_flat)
-        best_sd = {k: v.detach().cpu().clone() for k, v in model.state_dict().items()}
+        # one device-to-host copy of the flat buffer; the state_dict entries are views into it (94 separate .cpu() calls cost
+        # 94 synchronisations)
+        flat_cpu, base, esz = ft.flat.cpu(), ft.flat.data_ptr(), ft.flat.element_size()
+        best_sd = {}
+        for k, v in model.state_dict().items():
+            off = (v.data_ptr() - base) // esz
+            if v.dtype == ft.flat.dtype and v.is_contiguous() and 0 <= off and off + v.numel() <= flat_cpu.numel():
+                best_sd[k] = flat_cpu[off:off + v.numel()].view(v.shape).clone()
+            else:
+                best_sd[k] = v.detach().cpu().clone()
         ft.flat.copy_(final)
     return {"history": {"loss": h[:, 0].tolist(), "acc": h[:, 1].tolist(), "val_loss": h[:, 2].tolist(),
                         "val_acc": h[:, 3].tolist()},
@@ -225,6 +239,15 @@ def run_cv_jobs(config, jobs, load_subject, save_dir, max_epochs=200, batch_size
     file exists is skipped, so a crashed worker's jobs can simply be re-queued.  Returns the list of result dicts."""
     dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
     cache, done = {}, []
+    # a static shard knows its next subject: load it on a worker thread while this subject's folds train (the loaders
+    # release the GIL in NumPy / file I/O); a JobQueue hands jobs out one by one, so nothing to look ahead to
+    pending, pool, todo = {}, None, None
+    if isinstance(jobs, (list, tuple)):
+        from concurrent.futures import ThreadPoolExecutor
+        todo = [sid for _, sid, k in jobs
+                if not (resume and os.path.exists(os.path.join(save_dir, f"sub-{sid}", f"fold-{k}_result.json")))]
+        todo = [s_ for i, s_ in enumerate(todo) if i == 0 or todo[i - 1] != s_]        # subjects in the order they start
+        pool = ThreadPoolExecutor(max_workers=1)
     for si, sid, k in jobs:
         sub_dir = os.path.join(save_dir, f"sub-{sid}")
         os.makedirs(sub_dir, exist_ok=True)
@@ -234,8 +257,12 @@ def run_cv_jobs(config, jobs, load_subject, save_dir, max_epochs=200, batch_size
             continue
         if sid not in cache:
             cache.clear()                                      # one resident subject at a time per process
-            X, Y = load_subject(sid)
+            X, Y = pending.pop(sid).result() if sid in pending else load_subject(sid)
             cache[sid] = (torch.as_tensor(X).to(dev, non_blocking=True), torch.as_tensor(Y).to(dev, non_blocking=True))
+            if pool is not None and sid in todo:
+                nxt = todo.index(sid) + 1
+                if nxt < len(todo) and todo[nxt] not in pending:
+                    pending[todo[nxt]] = pool.submit(load_subject, todo[nxt])
         X, Y = cache[sid]
         tr_idx, va_idx = kfold_indices(X.shape[0], n_folds, True, seed)[k]
         out = train_fold(config, X, Y, tr_idx, va_idx, max_epochs, batch_size, job_seed(seed, n_folds, si, k), **fold_kw)
@@ -247,6 +274,8 @@ def run_cv_jobs(config, jobs, load_subject, save_dir, max_epochs=200, batch_size
             json.dump(res, f)
         os.replace(tmp, res_path)                              # the result file appears atomically = the job's commit
         done.append(res)
+    if pool is not None:
+        pool.shutdown(wait=True)
     return done
 
 
