@@ -569,12 +569,13 @@ def run_preprocess(args, rank, world, local_rank):
     value = total_trials * K / (ms * 1e-3)
     # end to end from pinned host memory
     xh = [x.cpu().pin_memory() for x in xs]
-    outh = [torch.empty(n_tr, 64, 636).pin_memory() for _ in xs]
+    for _ in F.bandpass_resample_host(xh, depth=3):       # warm-up: pinned output blocks enter the host allocator's cache
+        pass
     torch.cuda.synchronize(dev)
     e0.record()
-    for xi, oi in zip(xh, outh):
-        xd = xi.to(dev, non_blocking=True)
-        oi.copy_(F.sosfiltfilt_resample(sos, xd, 4, 5, out_dtype=torch.float32), non_blocking=True)
+    last = None
+    for oi in F.bandpass_resample_host(xh, depth=3):      # the public host-to-host call: copies overlap the kernel on side streams
+        last = oi
     e1.record()
     torch.cuda.synchronize(dev)
     e2e_ms = _max_over_ranks(e0.elapsed_time(e1), dist, dev)

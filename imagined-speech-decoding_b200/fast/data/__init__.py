@@ -17,7 +17,7 @@ from .preprocess import (
     load_subject_train_val,
     trials_from_mat,
 )
-from .filters import bandpass_sos, sosfiltfilt, resample_poly, sosfiltfilt_resample, bandpass_resample
+from .filters import bandpass_sos, sosfiltfilt, resample_poly, sosfiltfilt_resample, bandpass_resample, bandpass_resample_host
 
 __all__ = [
     "BasicDataset",
@@ -40,4 +40,5 @@ __all__ = [
     "resample_poly",
     "sosfiltfilt_resample",
     "bandpass_resample",
+    "bandpass_resample_host",
 ]

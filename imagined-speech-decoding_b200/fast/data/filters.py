@@ -79,6 +79,7 @@ def _kaiser_lowpass(up, down, beta=5.0):
 
 
 _FIR_CACHE = {}
+_STREAMS = {}
 
 
 def _fir_plan(device, up, down, window):
@@ -163,3 +164,42 @@ def bandpass_resample(x, fs=250.0, low=4.0, high=40.0, order=4, up=4, down=5, ou
     band-pass, then ``up/down`` polyphase resampling (250 -> 200 Hz by default).  The intermediate stays float64
     (in shared memory where the fused kernel applies)."""
     return sosfiltfilt_resample(bandpass_sos(order, low, high, fs), x, up, down, out_dtype=out_dtype)
+
+
+def bandpass_resample_host(blocks, fs=250.0, low=4.0, high=40.0, order=4, up=4, down=5, device=None, depth=2):
+    """Stream host blocks through ``bandpass_resample``: ``blocks`` is an iterable of host arrays / tensors (n, C, T)
+    float32 (pinned memory makes the copies asynchronous); block k+1 is copied in and block k-1 copied out while block k
+    is filtered, on ``depth`` CUDA streams (PCIe is full duplex, and the copies, not the kernel, are what a host-to-host
+    preprocessing run waits for).  Yields pinned float32 host tensors (n, C, T_out) in input order."""
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    sos = bandpass_sos(order, low, high, fs)
+    # the side streams are kept per device: the caching allocator pools blocks per stream, so fresh streams would cudaMalloc
+    # their staging tensors on every call
+    pool = _STREAMS.setdefault(dev, [])
+    while len(pool) < max(1, int(depth)):
+        pool.append(torch.cuda.Stream(dev))
+    streams = pool[:max(1, int(depth))]
+    cur = torch.cuda.current_stream(dev)
+    for s in streams:
+        s.wait_stream(cur)
+    inflight = []                                                    # (event, pinned output, tensors kept alive)
+    for k, blk in enumerate(blocks):
+        s = streams[k % len(streams)]
+        xh = torch.as_tensor(blk)
+        if xh.dtype != torch.float32:
+            xh = xh.float()
+        with torch.cuda.stream(s):
+            xd = xh.to(dev, non_blocking=True)
+            y = sosfiltfilt_resample(sos, xd, up, down, out_dtype=torch.float32)
+            out = torch.empty(y.shape, dtype=torch.float32, pin_memory=True)
+            out.copy_(y, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(s)
+        inflight.append((ev, out, (xh, xd, y)))
+        if len(inflight) >= len(streams):
+            ev0, out0, _ = inflight.pop(0)
+            ev0.synchronize()
+            yield out0
+    for ev0, out0, _ in inflight:
+        ev0.synchronize()
+        yield out0

@@ -366,6 +366,21 @@ def test_fused_filter_resample_equals_the_two_call_chain(filter_golden):
     assert torch.equal(p0, resample_poly(sosfiltfilt(sos, xd, padlen=0), 4, 5))
 
 
+def test_bandpass_resample_host_stream_equals_direct():
+    """The host-to-host streaming form (copies of neighbouring blocks overlap the kernel) returns, block for block and in
+    order, the bits of the direct call; ragged block sizes and an empty iterable are fine."""
+    from fast.data import bandpass_resample, bandpass_resample_host
+    g = torch.Generator().manual_seed(11)
+    blocks = [(torch.randn(n, 8, 795, generator=g) * 20).pin_memory() for n in (7, 1, 12, 5, 3)]
+    outs = list(bandpass_resample_host(blocks, depth=2))
+    assert len(outs) == len(blocks)
+    for b, o in zip(blocks, outs):
+        assert o.dtype == torch.float32 and o.device.type == "cpu" and o.shape == (b.shape[0], 8, 636)
+        assert torch.equal(o, bandpass_resample(b.cuda()).cpu())
+    assert torch.equal(next(iter(bandpass_resample_host([blocks[2].numpy()], depth=3))), outs[2])
+    assert list(bandpass_resample_host([])) == []
+
+
 def test_filter_properties_at_scale(filter_golden):
     """BASELINE config-3 sized batch: linearity and time-reversal symmetry of the zero-phase filter."""
     from fast.data import sosfiltfilt
