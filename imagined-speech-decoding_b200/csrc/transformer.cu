@@ -13,7 +13,7 @@
 
 namespace fb {
 
-constexpr int TR_THREADS = 256;
+constexpr int TR_THREADS = 512;
 constexpr int TR_WARPS = TR_THREADS / 32;
 constexpr float LN_EPS = 1e-5f;
 
