@@ -57,3 +57,40 @@ def test_argument_validation_without_a_gpu(libpath):
     assert rc < 0 and b"uint8 or int64" in lib.fastb200_last_error()
     with pytest.raises(RuntimeError, match="uint8 or int64"):
         N.check(rc, "ce")
+
+
+def test_fused_filter_support_predicate_is_host_logic(libpath):
+    """fastb200_sosfiltfilt_resample_supported runs no kernel: the 250 -> 200 Hz chain with scipy's default FIR and padlen is
+    the fused kernel's shape; another ratio, FIR alignment, a padlen shorter than the resampler's edge reach, or a row no
+    longer than padlen are not (the caller then chains the two kernels)."""
+    import numpy as np
+    from fast import _native as N
+    from fast.data.filters import _kaiser_lowpass
+    lib = N.lib()
+    dp = ctypes.POINTER(ctypes.c_double)
+
+    def fir(up, down, ntaps=None):
+        h = _kaiser_lowpass(up, down) if ntaps is None else np.hamming(ntaps) * up
+        half = (len(h) - 1) // 2
+        pre = down - half % down
+        hp = np.ascontiguousarray(np.concatenate([np.zeros(pre), h]))
+        return hp, (half + pre) // down
+
+    h, npr = fir(4, 5)
+    sup = lambda T, ns, pad, T_out, h_, up, down, npr_: lib.fastb200_sosfiltfilt_resample_supported(
+        T, ns, pad, T_out, h_.ctypes.data_as(dp), len(h_), up, down, npr_)
+    assert sup(795, 4, 27, 636, h, 4, 5, npr) == 1
+    assert sup(800, 4, 27, 640, h, 4, 5, npr) == 1
+    assert sup(795, 1, 27, 636, h, 4, 5, npr) == 1
+    assert sup(795, 4, 0, 636, h, 4, 5, npr) == 0            # no odd extension to hold the resampler's zero pads
+    assert sup(795, 4, 9, 636, h, 4, 5, npr) == 0            # 9 < the 13-sample reach of the 26-tap sub-filters
+    assert sup(27, 4, 27, 22, h, 4, 5, npr) == 0             # T must exceed padlen (scipy's ValueError)
+    assert sup(795, 5, 27, 636, h, 4, 5, npr) == 0           # more sections than the kernel carries
+    h54, npr54 = fir(5, 4)
+    assert sup(795, 4, 27, 994, h54, 5, 4, npr54) == 0       # other ratios take the two-kernel chain
+    h63, npr63 = fir(4, 5, 63)
+    assert sup(795, 4, 27, 636, h63, 4, 5, npr63) == 0       # a FIR whose centre lands on another polyphase alignment
+    h61, npr61 = fir(4, 5, 61)
+    assert sup(795, 4, 27, 636, h61, 4, 5, npr61) == 1       # same alignment as the default, fewer taps
+    rc = lib.fastb200_sosfiltfilt_resample(None, 4, None, 4, 0, 795, None, 4, 27, 636, None, 106, 4, 5, 11, None)
+    assert rc < 0 and b"NULL" in lib.fastb200_last_error()
