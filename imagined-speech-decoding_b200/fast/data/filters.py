@@ -3,7 +3,8 @@
 The reference repository has no filtering code; these functions are additive to ``fast.data``
 and follow ``scipy.signal.sosfiltfilt`` / ``scipy.signal.resample_poly`` semantics along the last axis.  The filter
 *design* (a handful of coefficients) is host arithmetic; every sample is touched only by the CUDA kernels
-``fastb200_sosfiltfilt`` / ``fastb200_resample_poly`` (include/fastb200.h).  There is no CPU fallback.
+``fastb200_sosfiltfilt`` / ``fastb200_resample_poly`` / ``fastb200_sosfiltfilt_resample`` (the chain in one kernel, the
+filtered float64 row never leaving shared memory) of include/fastb200.h.  There is no CPU fallback.
 """
 import ctypes as C
 import math
