@@ -176,7 +176,10 @@ def _f32c(t: torch.Tensor) -> torch.Tensor:
 class _HeadFn(torch.autograd.Function):
     """x (B,C,T) -> feat (B,n_win,Z,F): fastb200_head_pack / head_fwd; backward head_bwd / head_unpack_grad."""
 
+    # Under Lightning's `precision='bf16-mixed'` (scripts/train_fast.py:135,277) the model is called inside torch.autocast:
+    # the kernels are fp32-in / fp32-out, so autocast is switched off for the op and floating CUDA inputs arrive as fp32.
     @staticmethod
+    @torch.amp.custom_fwd(device_type='cuda', cast_inputs=torch.float32)
     def forward(ctx, x, desc, flat, offsets, step, grad_mode, *params):
         lib = N.lib()
         N.require_cuda(x, "input")
@@ -230,6 +233,7 @@ class _HeadFn(torch.autograd.Function):
         return feat
 
     @staticmethod
+    @torch.amp.custom_bwd(device_type='cuda')
     def backward(ctx, dfeat):
         lib = N.lib()
         desc, flat, xin = ctx.desc, ctx.flat, ctx.xin
@@ -262,6 +266,7 @@ class _TransformerFn(torch.autograd.Function):
     """feat (B,n_win,Z,F) -> logits (B,n_classes): fastb200_transformer_fwd / _bwd."""
 
     @staticmethod
+    @torch.amp.custom_fwd(device_type='cuda', cast_inputs=torch.float32)
     def forward(ctx, feat, desc, flat, offsets, used, mode, p_drop, seed, offset, grad_mode, *params):
         lib = N.lib()
         N.require_cuda(feat, "features")
@@ -286,6 +291,7 @@ class _TransformerFn(torch.autograd.Function):
         return logits
 
     @staticmethod
+    @torch.amp.custom_bwd(device_type='cuda')
     def backward(ctx, dlogits):
         lib = N.lib()
         desc, flat, fin = ctx.desc, ctx.flat, ctx.fin
@@ -387,6 +393,13 @@ class CVBlock(nn.Module):
         t = t + 2 * (self.Kc2 // 2) - self.Kc2 + 1
         t = t // 2
         self.flat_dim = self.F2 * t
+        # The reference sizes the projector by pushing an all-zero probe through the stack in TRAINING mode (fast.py:66-74), so
+        # a fresh module has already seen one batch of zeros in every BatchNorm: running_mean stays 0, running_var becomes
+        # (1 - momentum) * 1 + momentum * 0 and num_batches_tracked is 1.  Those buffers are part of the state_dict wire
+        # format and change eval-mode outputs, so reproduce the update (no RNG is consumed by it).
+        with torch.no_grad():
+            for bn in (self.bn1, self.bn2, self.bn3):
+                bn(torch.zeros(1, bn.num_features, 1, 2))
         self.projector = nn.Linear(self.flat_dim, dim_token)
 
     def forward(self, x):

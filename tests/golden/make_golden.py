@@ -8,6 +8,8 @@ scipy 1.18.1, and writes
 
     tests/golden/fast_golden.npz     model path: small config (full tensors) + production config
     tests/golden/filter_golden.npz   scipy sosfiltfilt / resample_poly outputs
+    tests/golden/alt_golden.npz      (``--alt`` only) the three alternative heads inside FAST, the test-set edge pad, and a
+                                     mock of Lightning's optimiser-then-scheduler loop over the reference's LambdaLR
 
 The GPU box has no /root/reference: tests read only the .npz files.  Inputs are regenerated in the
 tests from the seeds recorded here (torch CPU generator / numpy default_rng are deterministic for a
@@ -48,6 +50,81 @@ def probe(n, seed=12345):
 def fingerprint(t):
     a = t.detach().double().numpy().ravel()
     return np.array([a.sum(), np.abs(a).sum(), float(a @ probe(a.size)), np.abs(a).max()])
+
+
+def alt_main():
+    """Goldens added in round 2: alternative heads (reference fast.py:32-196) run inside the reference FAST, the test-set
+    edge pad (preprocess.py:110-114) and the LambdaLR step order (trainer.py:48-54).  Separate file so that the round-1
+    vectors stay byte-identical."""
+    from transformers import PretrainedConfig
+    ref_fast, _ = _import_reference()
+    out = {}
+    electrodes = ['Fp1', 'Fp2', 'F3', 'F4', 'C3', 'C4', 'O1', 'O2']
+    zones = {'Frontal': ['Fp1', 'Fp2', 'F3', 'F4'], 'Central': ['C3', 'C4'], 'Occipital': ['O1', 'O2']}
+    g = torch.Generator().manual_seed(21)
+    x = torch.randn(4, 8, 500, generator=g) * 2.0
+    y = torch.tensor([0, 2, 1, 1], dtype=torch.uint8)
+    out["x"], out["y"] = x.numpy(), y.numpy()
+    for head in ("CVBlock", "EEGNet_Encoder", "HeadConv_Paper_Version"):
+        cfg = PretrainedConfig(electrodes=electrodes, zone_dict=zones, dim_cnn=16, dim_token=16, seq_len=500,
+                               window_len=250, slide_step=125, head=head, n_classes=3, num_layers=1, num_heads=4,
+                               dropout=0.0)
+        torch.manual_seed(11)
+        m = ref_fast.FAST(cfg)
+        for k, v in m.state_dict().items():
+            out[f"{head}/sd0/{k}"] = v.numpy().copy()                 # fresh state_dict incl. BatchNorm buffers
+        out[f"{head}/eval0_logits"] = m.eval()(x).detach().numpy()    # eval mode on the fresh running statistics
+        m.train()
+        for mod in m.modules():                                       # the heads carry their own Dropout(p>0): switch it off
+            if isinstance(mod, torch.nn.Dropout):
+                mod.p = 0.0
+        logits = m(x)
+        loss = torch.nn.CrossEntropyLoss()(logits, y)
+        loss.backward()
+        out[f"{head}/train_logits"] = logits.detach().numpy()
+        out[f"{head}/loss"] = loss.detach().numpy()
+        for k, p in m.named_parameters():
+            out[f"{head}/grad/{k}"] = p.grad.numpy().copy()
+        for k, v in m.state_dict().items():
+            if "running_" in k or "num_batches" in k:
+                out[f"{head}/sd1/{k}"] = v.numpy().copy()             # BatchNorm running statistics after one train step
+        out[f"{head}/eval1_logits"] = m.eval()(x).detach().numpy()
+        out[f"{head}/feat_eval"] = m.forward_head(x).detach().numpy()
+
+    # test-set edge pad, (N, C, T) layout as the v7.3 files hold it (preprocess.py:110-114)
+    rng = np.random.default_rng(9)
+    xt = rng.standard_normal((5, 64, 795)) * 25.0
+    pad_width = 800 - xt.shape[2]
+    xp = np.pad(xt, ((0, 0), (0, 0), (0, pad_width)), 'edge').astype(np.float32)
+    out["pad/sha"] = np.array(sha(xp))
+    out["pad/tail"] = xp[3, 7, 790:].copy()
+
+    # LambdaLR order: the reference's scheduler indexes cosine_lr_list[global_step - 1] and Lightning steps the optimiser,
+    # increments global_step, then steps the scheduler (interval='step').  Mock of exactly that loop over torch's LambdaLR.
+    sys.modules.setdefault("torchmetrics", types.ModuleType("torchmetrics"))
+    sched_src = open("/root/reference/src/fast/train/trainer.py").read().split("class EEG_Encoder_Module")[0]
+    ns = {}
+    exec(compile(sched_src.replace("import torchmetrics", "").replace("import lightning as pl", "")
+                 .replace("from ..models import FAST", ""), "trainer_head", "exec"), ns)
+    lst = ns["cosine_scheduler"](1, 0.1, 12, 3, warmup_epochs=10)
+
+    class Mod:
+        global_step = 0
+    mod = Mod()
+    p = torch.nn.Parameter(torch.zeros(3))
+    opt = torch.optim.AdamW([p], lr=0.0005)
+    sch = torch.optim.lr_scheduler.LambdaLR(opt, lambda epoch: lst[mod.global_step - 1])
+    used = []
+    for _ in range(len(lst)):
+        used.append(opt.param_groups[0]["lr"])
+        p.grad = torch.ones(3)
+        opt.step()
+        mod.global_step += 1
+        sch.step()
+    out["lr/list"] = np.asarray(lst)
+    out["lr/used"] = np.asarray(used)
+    np.savez_compressed(os.path.join(HERE, "alt_golden.npz"), **out)
+    print("wrote alt_golden.npz", os.path.getsize(os.path.join(HERE, "alt_golden.npz")))
 
 
 def main():
@@ -204,4 +281,7 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    if "--alt" in sys.argv:
+        alt_main()
+    else:
+        main()

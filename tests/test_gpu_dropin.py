@@ -1,0 +1,224 @@
+"""Round-2 parity tests of the drop-in surface around the hot path (all through the CUDA kernels / C ABI):
+
+* the three alternative heads inside FAST (reference fast.py:32-196) against goldens generated from the real reference
+  (tests/golden/make_golden.py --alt): fresh state_dict incl. BatchNorm buffers, eval and train mode, running statistics
+  after one step;
+* ``inference_on_loader`` and ``EEG_Encoder_Module.training_step / validation_step / configure_optimizers``
+  (reference src/fast/train/trainer.py:30-93) against the CPU oracle loop;
+* the test-set edge pad (reference src/fast/data/preprocess.py:110-114), bit exact;
+* the model under ``torch.autocast('cuda', torch.bfloat16)`` (the reference's ``precision='bf16-mixed'``,
+  scripts/train_fast.py:135,277): fp32 logits and gradients within the same 1e-4.
+"""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import ROOT, make_prod_cfg, make_small_cfg, rel_err
+from oracle import fast_oracle as O
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+@pytest.fixture(scope="module")
+def alt():
+    return np.load(os.path.join(ROOT, "tests", "golden", "alt_golden.npz"))
+
+
+@pytest.fixture()
+def no_tf32():
+    """The alternative heads are stock cuDNN / cuBLAS composites: keep them in full fp32 for the 1e-4 comparison."""
+    old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    yield
+    torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
+
+
+# ---------------------------------------------------------------------------------------------- alternative heads
+@pytest.mark.parametrize("head", ["CVBlock", "EEGNet_Encoder", "HeadConv_Paper_Version"])
+def test_alternative_heads_inside_fast_vs_reference(alt, head, no_tf32):
+    from fast.models import FAST
+    torch.manual_seed(11)
+    m = FAST(make_small_cfg(head=head))
+    sd = m.state_dict()
+    for k, v in sd.items():                                         # same RNG stream AND the probe's BatchNorm side effect
+        assert torch.equal(v, torch.from_numpy(alt[f"{head}/sd0/{k}"])), k
+    m = m.cuda()
+    x, y = torch.from_numpy(alt["x"]).cuda(), torch.from_numpy(alt["y"]).cuda()
+    with torch.no_grad():
+        assert rel_err(m.eval()(x), alt[f"{head}/eval0_logits"]) < TOL
+    m.train()
+    for mod in m.modules():
+        if isinstance(mod, torch.nn.Dropout):
+            mod.p = 0.0
+    logits = m(x)
+    loss = torch.nn.CrossEntropyLoss()(logits, y)
+    loss.backward()
+    assert rel_err(logits, alt[f"{head}/train_logits"]) < TOL
+    assert abs(float(loss) - float(alt[f"{head}/loss"])) < 1e-5
+    for k, p in m.named_parameters():
+        ref = alt[f"{head}/grad/{k}"]
+        assert p.grad is not None, k
+        if np.abs(ref).max() < 1e-7:        # conv weights/biases directly in front of a BatchNorm: the true gradient is 0
+            assert float(p.grad.abs().max()) < 1e-5, k
+        else:
+            # cuDNN's BatchNorm / conv backward reassociates; 5e-4 of the tensor's max on these stock composites
+            assert rel_err(p.grad, ref) < 5e-4, (k, rel_err(p.grad, ref))
+    for k, v in m.state_dict().items():
+        if "running_" in k:
+            assert rel_err(v, alt[f"{head}/sd1/{k}"]) < TOL, k
+        elif "num_batches" in k:
+            assert int(v) == int(alt[f"{head}/sd1/{k}"]), k
+    with torch.no_grad():
+        m.eval()
+        assert rel_err(m(x), alt[f"{head}/eval1_logits"]) < TOL
+        assert rel_err(m.forward_head(x), alt[f"{head}/feat_eval"]) < TOL
+
+
+# ---------------------------------------------------------------------------------------------- trainer-facing module
+def _batches(n, b, seed):
+    g = torch.Generator().manual_seed(seed)
+    return [(torch.randn(b, 64, 800, generator=g) * 2, torch.randint(0, 5, (b,), generator=g).to(torch.uint8)) for _ in range(n)]
+
+
+def test_inference_on_loader_matches_oracle():
+    from fast.data import BasicDataset
+    from fast.models import FAST
+    from fast.train import inference_on_loader
+    cfg = make_prod_cfg()
+    torch.manual_seed(42)
+    m = FAST(cfg)
+    sd = {k: v.detach().clone() for k, v in m.state_dict().items()}
+    g = torch.Generator().manual_seed(5)
+    X = (torch.randn(21, 64, 800, generator=g) * 30).numpy()        # x30: the head dominates the logits
+    Y = torch.randint(0, 5, (21,), generator=g).to(torch.uint8).numpy()
+    loader = torch.utils.data.DataLoader(BasicDataset(X, Y), batch_size=8, shuffle=False)       # 8, 8, 5: a ragged tail
+    pred, real = inference_on_loader(m, loader)
+    assert pred.dtype == np.int64 and pred.shape == (21,) and real.dtype == np.uint8
+    assert np.array_equal(real, Y)
+    with torch.no_grad():
+        ref = O.forward(sd, cfg, torch.from_numpy(X))
+    top2 = ref.topk(2, dim=1).values
+    clear = (top2[:, 0] - top2[:, 1]) > 1e-4 * ref.abs().max()       # argmax is only defined up to the parity tolerance
+    assert clear.sum() >= 15
+    assert np.array_equal(pred[clear.numpy()], ref.argmax(1).numpy()[clear.numpy()])
+    assert not m.training and next(m.parameters()).is_cuda           # the reference leaves the model in eval mode on the GPU
+
+
+def test_confusion_metric_vs_sklearn():
+    from sklearn.metrics import accuracy_score, f1_score
+    from fast.train.trainer import _ConfusionMetric
+    g = torch.Generator().manual_seed(3)
+    acc, f1 = _ConfusionMetric(5, 'accuracy').cuda(), _ConfusionMetric(5, 'f1').cuda()
+    all_p, all_t = [], []
+    for n in (64, 64, 24):
+        logits = torch.randn(n, 5, generator=g)
+        t = torch.randint(0, 4, (n,), generator=g)                   # class 4 never a target: exercises the 'absent class' rule
+        a, f = acc(logits.cuda(), t.cuda()), f1(logits.cuda(), t.cuda())
+        p = logits.argmax(1).numpy()
+        assert abs(float(a) - accuracy_score(t.numpy(), p)) < 1e-6
+        # torchmetrics' macro F1 averages over classes present in target or prediction = sklearn over those labels
+        labels = np.union1d(t.numpy(), p)
+        assert abs(float(f) - f1_score(t.numpy(), p, average='macro', labels=labels)) < 1e-6
+        all_p.append(p); all_t.append(t.numpy())
+    P, T = np.concatenate(all_p), np.concatenate(all_t)
+    assert abs(float(acc.compute()) - accuracy_score(T, P)) < 1e-6
+    assert abs(float(f1.compute()) - f1_score(T, P, average='macro', labels=np.union1d(T, P))) < 1e-6
+    acc.reset()
+    assert int(acc.confusion.sum()) == 0
+
+
+def test_eeg_encoder_module_steps_match_oracle_loop():
+    """training_step -> backward -> AdamW.step -> global_step += 1 -> LambdaLR.step (Lightning's order for
+    interval='step'), three steps, against the oracle's loss_and_grads + adamw_step at the lr the scheduler really applies."""
+    from fast.train import EEG_Encoder_Module
+    from fast.train.fused import lightning_lr_factors
+    cfg = make_prod_cfg(dropout=0.0)
+    torch.manual_seed(42)
+    mod = EEG_Encoder_Module(cfg, max_epochs=12, niter_per_ep=2).cuda()
+    mod.train()
+    assert isinstance(mod.loss, torch.nn.CrossEntropyLoss) and len(mod.cosine_lr_list) == 24
+    sd = {k: v.detach().cpu().clone() for k, v in mod.model.state_dict().items()}
+    mom = {k: torch.zeros_like(v) for k, v in sd.items()}
+    var = {k: torch.zeros_like(v) for k, v in sd.items()}
+    (opt,), (sch,) = mod.configure_optimizers()
+    assert isinstance(opt, torch.optim.AdamW) and opt.defaults["lr"] == 0.0005 and opt.defaults["weight_decay"] == 0.01
+    assert sch["interval"] == "step"
+    assert len(opt.param_groups[0]["params"]) == 94
+    factors = lightning_lr_factors(mod.cosine_lr_list)
+    batches = _batches(3, 8, 17)
+    for step, (x, y) in enumerate(batches, 1):
+        assert abs(opt.param_groups[0]["lr"] - 5e-4 * factors[step - 1]) < 1e-12        # what Lightning would run this step at
+        opt.zero_grad()
+        loss = mod.training_step((x.cuda(), y.cuda()), step - 1)
+        assert loss.dim() == 0 and float(loss) > 0
+        loss.backward()
+        opt.step()
+        mod.global_step += 1
+        sch["scheduler"].step()
+        ref_loss, ref_logits, grads, _ = O.loss_and_grads(sd, cfg, x, y)
+        assert abs(float(loss) - float(ref_loss)) < 2e-5
+        assert abs(float(mod.logged["train_loss"]) - float(ref_loss)) < 2e-5
+        assert abs(float(mod.logged["train_acc"]) - float((ref_logits.argmax(1) == y.long()).float().mean())) < 1e-6
+        for k in sd:
+            O.adamw_step(sd[k], grads[k], mom[k], var[k], step, 5e-4 * factors[step - 1])
+    # validation_step: loss + accumulating metrics, no dropout, on the updated weights
+    mod.eval()
+    x, y = batches[0]
+    with torch.no_grad():
+        vloss = mod.validation_step((x.cuda(), y.cuda()), 0)
+        ref = O.forward(sd, cfg, x)
+    ref_v = O.cross_entropy_mean(ref, y)
+    assert abs(float(vloss) - float(ref_v)) < 5e-5
+    assert abs(float(mod.logged["val_loss"]) - float(ref_v)) < 5e-5
+    assert 0.0 <= float(mod.logged["val_acc"]) <= 1.0
+    assert int(mod.val_f1.confusion.sum()) == 8 and int(mod.val_acc.confusion.sum()) == 8
+
+
+# ---------------------------------------------------------------------------------------------- data: test-set pad (P2)
+def test_pad_edge_ncT_bit_exact(alt):
+    from fast.data.preprocess import _pad_edge_ncT
+    rng = np.random.default_rng(9)
+    xt = rng.standard_normal((5, 64, 795)) * 25.0
+    out = _pad_edge_ncT(xt, 800)
+    assert out.shape == (5, 64, 800) and out.dtype == torch.float32
+    assert hashlib.sha256(out.cpu().contiguous().numpy().tobytes()).hexdigest() == str(alt["pad/sha"])
+    assert np.array_equal(out[3, 7, 790:].cpu().numpy(), alt["pad/tail"])
+    ref = np.pad(xt, ((0, 0), (0, 0), (0, 5)), 'edge').astype(np.float32)          # preprocess.py:110-114
+    assert np.array_equal(out.cpu().numpy(), ref)
+    # float32 input, already long enough: unchanged apart from the dtype
+    x32 = xt.astype(np.float32)[:, :, :20]
+    assert np.array_equal(_pad_edge_ncT(x32, 16).cpu().numpy(), x32)
+
+
+# ---------------------------------------------------------------------------------------------- autocast (bf16-mixed)
+def test_forward_backward_under_bf16_autocast(golden):
+    from fast.models import FAST
+    torch.manual_seed(42)
+    cfg = make_prod_cfg(dropout=0.0)
+    m = FAST(cfg).cuda().train()
+    x = torch.randn(4, 64, 800, generator=torch.Generator().manual_seed(43))
+    y = torch.from_numpy(golden["prod/y"])
+    with torch.autocast('cuda', dtype=torch.bfloat16):
+        logits = m(x.cuda())
+        feat = m.forward_head(x.cuda())
+        loss = torch.nn.CrossEntropyLoss()(logits.float(), y.cuda())
+    assert logits.dtype == torch.float32 and feat.dtype == torch.float32       # kernels are fp32-in / fp32-out: no bf16 output
+    loss.backward()
+    assert rel_err(logits, golden["prod/logits"]) < TOL
+    assert rel_err(feat, golden["prod/feat"]) < TOL
+    keys = [str(k) for k in golden["prod/grad_keys"]]
+    named = dict(m.named_parameters())
+    for k in keys:
+        gk = f"prod/grad/{k}"
+        if gk in golden.files:
+            assert named[k].grad.dtype == torch.float32
+            assert rel_err(named[k].grad, golden[gk]) < TOL, k
+    # a bf16 INPUT (what an upstream autocast op would hand over) is cast, not rejected
+    with torch.autocast('cuda', dtype=torch.bfloat16), torch.no_grad():
+        lb = m(x.cuda().bfloat16())
+    assert lb.dtype == torch.float32 and rel_err(lb, golden["prod/logits"]) < 2e-2

@@ -103,12 +103,58 @@ def test_alternative_heads_construct():
         assert not m.head._fused and len(m.head.encoders) == 3
 
 
+def test_alternative_heads_fresh_state_dict_equals_reference():
+    """Same RNG stream AND the BatchNorm side effect of the reference's zero probe in CVBlock.__init__ (fast.py:66-74:
+    running_var = 0.9, num_batches_tracked = 1), bit for bit against the real reference's fresh state_dict."""
+    import os
+    from conftest import ROOT
+    from fast.models import FAST
+    alt = np.load(os.path.join(ROOT, "tests", "golden", "alt_golden.npz"))
+    for head in ("CVBlock", "EEGNet_Encoder", "HeadConv_Paper_Version"):
+        torch.manual_seed(11)
+        sd = FAST(make_small_cfg(head=head)).state_dict()
+        ref_keys = [k[len(head) + 5:] for k in alt.files if k.startswith(head + "/sd0/")]
+        assert list(sd.keys()) == ref_keys, head
+        for k, v in sd.items():
+            assert torch.equal(v, torch.from_numpy(alt[f"{head}/sd0/{k}"])), (head, k)
+    from fast.models import CVBlock
+    b = CVBlock(4, 16)
+    assert float(b.bn1.running_var[0]) == float(torch.tensor(0.9)) and int(b.bn3.num_batches_tracked) == 1
+    assert float(b.bn2.running_mean.abs().max()) == 0.0
+
+
 def test_lr_factor_order():
     from fast.train import cosine_scheduler
     from fast.train.fused import lightning_lr_factors
     s = cosine_scheduler(1, 0.1, 200, 5, warmup_epochs=10)
     f = lightning_lr_factors(s)
     assert len(f) == len(s) and f[0] == s[-1] and f[1] == 0.0 and f[2] == s[1]
+
+
+def test_lr_factor_order_pinned_by_lambdalr_mock():
+    """tests/golden/make_golden.py --alt ran the reference's LambdaLR (trainer.py:50-53) through Lightning's
+    optimiser.step -> global_step += 1 -> scheduler.step loop; lightning_lr_factors must give the lr of every step."""
+    import os
+    from conftest import ROOT
+    from fast.train import cosine_scheduler
+    from fast.train.fused import lightning_lr_factors
+    alt = np.load(os.path.join(ROOT, "tests", "golden", "alt_golden.npz"))
+    lst = cosine_scheduler(1, 0.1, 12, 3, warmup_epochs=10)
+    np.testing.assert_array_equal(lst, alt["lr/list"])
+    np.testing.assert_allclose(5e-4 * lightning_lr_factors(lst), alt["lr/used"], rtol=0, atol=1e-18)
+    # and live, with the drop-in module's own scheduler object (no Lightning needed for the arithmetic)
+    from fast.train import EEG_Encoder_Module
+    mod = EEG_Encoder_Module(make_small_cfg(), max_epochs=12, niter_per_ep=3)
+    if isinstance(getattr(type(mod), "global_step", None), property):
+        return                                  # a real LightningModule owns global_step; the mock loop above already pinned it
+    (opt,), (sch,) = mod.configure_optimizers()
+    used = []
+    for _ in range(len(lst)):
+        used.append(opt.param_groups[0]["lr"])
+        opt.step()
+        mod.global_step += 1
+        sch["scheduler"].step()
+    np.testing.assert_allclose(used, alt["lr/used"], rtol=0, atol=1e-18)
 
 
 def test_filter_design_helpers(filter_golden):
