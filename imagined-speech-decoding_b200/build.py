@@ -21,6 +21,9 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC",
     "-I", os.path.join(ROOT, "include"), "-I", CSRC,
 ]
+# developer builds: FASTB200_NVCC_EXTRA="-DFASTB200_PROFILE -DFASTB200_DEBUG" adds the instrumented kernels, the
+# fastb200_debug_set_tc_profile entry point and the environment tuning knobs (none of which ship by default)
+NVCC_FLAGS += os.environ.get("FASTB200_NVCC_EXTRA", "").split()
 
 
 def sources():

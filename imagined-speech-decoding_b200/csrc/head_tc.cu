@@ -554,10 +554,13 @@ extern "C" int fastb200_head_pack_tc(const fastb200_model* m, const float* param
     return check_launch("head_pack_tc");
 }
 
-// Diagnostic buffer for the next fastb200_head_fwd_tc calls of this thread (148 x 8 int64 wait-cycle counters per launch);
-// NULL (default) = uninstrumented kernel.  Not part of the product path.
+#ifdef FASTB200_PROFILE
+// Developer builds only (nvcc -DFASTB200_PROFILE): diagnostic buffer for the next fastb200_head_fwd_tc calls of this thread
+// (148 x 16 int64 wait-cycle counters per launch); NULL = uninstrumented kernel.  The shipped library neither exports this
+// symbol nor instantiates the instrumented kernels nor reads the environment.
 static thread_local long long* g_tc_prof = nullptr;
 extern "C" void fastb200_debug_set_tc_profile(long long* dev_buf) { g_tc_prof = dev_buf; }
+#endif
 
 static int head_fwd_tc_launch(const fastb200_model* m, const void* packed, const float* x, int B, int T, int n_win,
                               int step, float* feat, float* saved, int n_terms, void* stream) {
@@ -567,9 +570,12 @@ static int head_fwd_tc_launch(const fastb200_model* m, const void* packed, const
     FB_REQUIRE((int64_t)B * n_win < (1ll << 31) / FASTB200_MAX_ZONES, "too many items for one launch");
     if (B == 0) return 0;
     tc::FwdArgs a;
-    a.packed = static_cast<const uint8_t*>(packed); a.x = x; a.feat = feat; a.prof = g_tc_prof;
+    a.packed = static_cast<const uint8_t*>(packed); a.x = x; a.feat = feat; a.prof = nullptr; a.dbg = 0;
     a.saved = saved; a.TS = head_saved_stride(m->window_len);
+#ifdef FASTB200_PROFILE
+    a.prof = g_tc_prof;
     a.dbg = (g_tc_prof && getenv("FASTB200_TC_DBG")) ? atoi(getenv("FASTB200_TC_DBG")) : 0;
+#endif
     a.B = B; a.T = T; a.n_win = n_win; a.step = step; a.C = m->n_chan; a.W = m->window_len; a.Z = m->n_zones;
     a.T_out = m->window_len - 4; a.split = a.T_out / 2; a.tb1 = a.T_out - 128;
     int n_sel = 0;
@@ -613,7 +619,9 @@ static int head_fwd_tc_launch(const fastb200_model* m, const void* packed, const
     if (e != cudaSuccess) return fail((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));                 \
     tc::head_fwd_tc_kernel<NTT, PROFF, SAVEE><<<grid, tc::THREADS, smem, as_stream(stream)>>>(a);
     if (saved)       { if (n_terms == 2) { LAUNCH_TC(2, false, true) } else { LAUNCH_TC(3, false, true) } }
+#ifdef FASTB200_PROFILE
     else if (a.prof) { if (n_terms == 2) { LAUNCH_TC(2, true, false) } else { LAUNCH_TC(3, true, false) } }
+#endif
     else             { if (n_terms == 2) { LAUNCH_TC(2, false, false) } else { LAUNCH_TC(3, false, false) } }
 #undef LAUNCH_TC
     return check_launch("head_fwd_tc");

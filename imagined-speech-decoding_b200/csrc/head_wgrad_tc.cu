@@ -61,7 +61,7 @@ struct Args {
     int n_win, step, C, T, W;
     int cz[FASTB200_MAX_ZONES], zoff[FASTB200_MAX_ZONES], boff[FASTB200_MAX_ZONES];   // zone size / offset into chan / packed beff offset
     int chan[FASTB200_MAX_CHANS];
-    uint32_t desc_hi, lbo16;                   // descriptor high word / LBO in 16-byte units (debug: FASTB200_WG_SWAP swaps LBO and SBO)
+    uint32_t desc_hi, lbo16;                   // descriptor high word / LBO in 16-byte units
     int goff[FASTB200_MAX_ZONES][3];           // float offset of the packed cnn3 / cnn4 / collapsed-embed gradient block of zone z
     uint8_t cta_zone[NUM_SMS], cta_layer[NUM_SMS], cta_rank[NUM_SMS], cta_n[NUM_SMS];
 };
@@ -291,15 +291,25 @@ extern "C" int fastb200_head_bwd_tc(const fastb200_model* m, const float* packed
                                     const float* dfeat, int B, int T, int n_win, int step, float* gpacked, float* dx,
                                     float* work, void* stream) {
     if (int r = wgrad_tc_supported(m)) return r;
+    FB_REQUIRE(B >= 0 && n_win >= 1 && step >= 1, "bad B/n_win/step");
+    FB_REQUIRE((n_win - 1) * (int64_t)step + m->window_len <= T, "windows run past the trial: n_win=%d step=%d W=%d T=%d", n_win, step, m->window_len, T);
+    FB_REQUIRE((int64_t)B * n_win < (1ll << 31) / FASTB200_MAX_ZONES, "too many items for one launch");
     if (B == 0) return 0;
+    FB_REQUIRE(packed && x && saved && dfeat && gpacked, "head_bwd_tc: NULL buffer");
     FB_REQUIRE(work != nullptr, "head_bwd_tc needs its workspace (fastb200_head_bwd_tc_work_floats)");
     // the collapsed-embed weight / bias gradients join the tensor-core kernel when no input gradient is wanted (training) and
     // every zone fits the 16-channel electrode tile; otherwise the CUDA-core kernel keeps them (and dx)
     bool embed_tc = dx == nullptr;
     for (int z = 0; z < m->n_zones; ++z) embed_tc = embed_tc && m->zone_size[z] <= 16;
-    const char* dg_env = getenv("FASTB200_DGRAD");                                    // debug: "ffma" forces the CUDA-core chain
-    const int dg_terms = (dg_env && atoi(dg_env) == 3) ? 3 : 2;
-    if (embed_tc && head_dgrad_tc_supported(m) && !(dg_env && dg_env[0] == 'f')) {
+    int dg_terms = 2;
+    bool dg_ffma = false;
+#ifdef FASTB200_DEBUG
+    if (const char* dg_env = getenv("FASTB200_DGRAD")) {                              // developer builds: "ffma" forces the CUDA-core chain, "3" = 3 terms
+        dg_ffma = dg_env[0] == 'f';
+        if (atoi(dg_env) == 3) dg_terms = 3;
+    }
+#endif
+    if (embed_tc && head_dgrad_tc_supported(m) && !dg_ffma) {
         float* pk = work + (int64_t)B * n_win * m->n_zones * 3 * m->dim_cnn * head_saved_stride(m->window_len);
         if (int r = head_dgrad_tc_launch(m, packed, saved, dfeat, B, n_win, work, pk, dg_terms, stream)) return r;
     } else if (int r = head_dgrad_launch(m, packed, x, saved, dfeat, B, T, n_win, step, gpacked, dx, work, embed_tc ? 1 : 0, stream)) return r;
@@ -309,7 +319,6 @@ extern "C" int fastb200_head_bwd_tc(const fastb200_model* m, const float* packed
     a.ksteps = ceil_div(a.T_out, 16);
     a.n_win = n_win; a.step = step; a.C = m->n_chan; a.T = T; a.W = m->window_len;
     a.desc_hi = wg::DESC_HI_MN; a.lbo16 = 128u >> 4;
-    if (const char* sw = getenv("FASTB200_WG_SWAP")) if (atoi(sw)) { a.desc_hi = (128u >> 4) | (1u << 14); a.lbo16 = (uint32_t)(wg::PLANE >> 4); }
     int n_sel = 0;
     for (int z = 0; z < m->n_zones; ++z) {
         const PackedZone p = packed_zone(*m, z);

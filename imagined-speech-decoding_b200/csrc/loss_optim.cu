@@ -7,15 +7,29 @@
 namespace fb {
 
 // One CTA; thread per trial, block-level tree reduction for the mean (deterministic).
+// Labels follow nn.CrossEntropyLoss (trainer.py:37,59): a target of -100 (torch's default ignore_index; int64 labels only)
+// takes no part in the loss, the mean or the gradient; any other label outside [0, NC) is an error that torch reports with a
+// device-side assert -- here the loss and that row's gradient become NaN (loud at the job's single host read, and no
+// out-of-bounds access), since the launch may sit inside a captured graph where nothing can be raised.
 template <typename LabelT>
 __global__ void ce_kernel(const float* __restrict__ logits, const LabelT* __restrict__ labels, int B, int NC,
                           float grad_scale, float* __restrict__ loss, float* __restrict__ dlogits,
                           int64_t* __restrict__ pred, int32_t* __restrict__ n_correct) {
     __shared__ float s_loss[32];
     __shared__ int s_hit[32];
+    __shared__ int s_cnt;
     float my_loss = 0.f;
-    int my_hit = 0;
-    const float gs = grad_scale / (float)B;
+    int my_hit = 0, my_cnt = 0;
+    if (threadIdx.x == 0) s_cnt = 0;
+    __syncthreads();
+    for (int r = threadIdx.x; r < B; r += blockDim.x) my_cnt += ((long long)labels[r] != -100ll);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) my_cnt += __shfl_xor_sync(0xffffffffu, my_cnt, o);
+    if ((threadIdx.x & 31) == 0 && my_cnt) atomicAdd(&s_cnt, my_cnt);          // integer: order-independent
+    __syncthreads();
+    const int n_used = s_cnt;                                  // torch divides by the number of non-ignored targets
+    const float gs = grad_scale / (float)n_used;
+    const float qnan = __int_as_float(0x7fc00000);
     for (int r = threadIdx.x; r < B; r += blockDim.x) {
         const float* l = logits + (size_t)r * NC;
         float mx = l[0];
@@ -25,14 +39,21 @@ __global__ void ce_kernel(const float* __restrict__ logits, const LabelT* __rest
         float se = 0.f;
         for (int c = 0; c < NC; ++c) se += expf(l[c] - mx);
         const float lse = mx + logf(se);
-        const int y = (int)labels[r];
-        my_loss += lse - l[y];
-        my_hit += (am == y);
+        const long long yl = (long long)labels[r];
+        const bool ignored = yl == -100ll;
+        const bool bad = !ignored && (yl < 0 || yl >= NC);
+        const int y = (ignored || bad) ? 0 : (int)yl;
+        if (!ignored) {
+            my_loss += bad ? qnan : lse - l[y];
+            my_hit += (!bad && am == y);
+        }
         if (pred) pred[r] = am;
         if (dlogits) {
             const float inv = 1.0f / se;
-            for (int c = 0; c < NC; ++c)
-                dlogits[(size_t)r * NC + c] = (expf(l[c] - mx) * inv - (c == y ? 1.f : 0.f)) * gs;
+            for (int c = 0; c < NC; ++c) {
+                const float d = (expf(l[c] - mx) * inv - (c == y ? 1.f : 0.f)) * gs;
+                dlogits[(size_t)r * NC + c] = ignored ? 0.f : (bad ? qnan : d);
+            }
         }
     }
     my_loss = warp_sum(my_loss);
@@ -49,7 +70,7 @@ __global__ void ce_kernel(const float* __restrict__ logits, const LabelT* __rest
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) h += __shfl_xor_sync(0xffffffffu, h, o);
         if (lane == 0) {
-            if (loss) *loss = v / (float)B;
+            if (loss) *loss = v / (float)n_used;               // 0 / 0 = NaN when every target is ignored, as torch
             if (n_correct) *n_correct = h;
         }
     }

@@ -661,7 +661,9 @@ template <typename SizeFn>
 static int pick_group(const fastb200_model& m, int B, int tok, int n_win, SizeFn size_fn, size_t budget) {
     int G = 1;
     int want = ceil_div(B, 2 * NUM_SMS);
-    if (const char* e = getenv("FASTB200_TR_GROUP")) want = atoi(e) > 0 ? atoi(e) : want;     // tuning probe
+#ifdef FASTB200_DEBUG
+    if (const char* e = getenv("FASTB200_TR_GROUP")) want = atoi(e) > 0 ? atoi(e) : want;     // developer builds: tuning probe
+#endif
     while (G < want && G < 16 && size_fn(m, G + 1, tok, n_win) * sizeof(float) <= budget) ++G;
     return G;
 }

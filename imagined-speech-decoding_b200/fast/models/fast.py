@@ -108,10 +108,14 @@ class _FlatParams:
         ok = flat is not None
         if ok:
             base = flat.data_ptr()
-            for _, p, off, _ in self.items:
-                if p.data_ptr() != base + 4 * off:
+            n = 0
+            for (_, p, off, _), q in zip(self.items, self.module.parameters()):
+                # `q is not p`: load_state_dict(assign=True) / direct attribute assignment swapped the Parameter object
+                if q is not p or p.data_ptr() != base + 4 * off:
                     ok = False
                     break
+                n += 1
+            ok = ok and n == len(self.items)
         if not ok:
             self._collect()
             first = self.items[0][1]
@@ -120,6 +124,18 @@ class _FlatParams:
                     raise RuntimeError(f"parameter {name} is {p.dtype}: the FAST kernels are fp32-only")
                 if p.device != first.device:
                     raise RuntimeError("all FAST parameters must live on one device")
+            # A sub-module (Head, Conv4Layers called on their own) whose parameters already sit back to back inside an
+            # owner's flat buffer adopts that range as its own flat view: re-flattening would pull the parameters OUT of the
+            # owner's buffer and orphan whatever holds it (a FusedTrainer, a captured graph).
+            base = first.data_ptr()
+            if all(p.data_ptr() == base + 4 * off and p.is_contiguous() for _, p, off, _ in self.items) and \
+                    first.untyped_storage().nbytes() >= first.storage_offset() * 4 + 4 * self.total:
+                with torch.no_grad():
+                    flat = torch.as_strided(first.detach(), (self.total,), (1,), first.storage_offset())
+                if all(p.untyped_storage().data_ptr() == first.untyped_storage().data_ptr() for _, p, _, _ in self.items):
+                    self.flat = flat
+                    self.version += 1
+                    return flat
             with torch.no_grad():
                 flat = torch.cat([p.detach().reshape(-1) for _, p, _, _ in self.items])
                 for _, p, off, n in self.items:

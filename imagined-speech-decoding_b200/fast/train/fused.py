@@ -47,6 +47,7 @@ class FusedTrainer:
         N.require_cuda(flat, "model parameters")
         self.device = flat.device
         self.flat, self.desc = flat, desc
+        self._flat_version = model._fp.version
         self.forward_mode = forward_mode
         self.mode = N.MODE_TRAIN_HEAD if forward_mode == 'train_head' else N.MODE_DEFAULT
         self.freeze_head = forward_mode == 'train_transformer'
@@ -89,16 +90,37 @@ class FusedTrainer:
             self._snapshot = flat.clone()
 
     # ------------------------------------------------------------------------------------------ workspaces
+    def _p_drop_now(self):
+        return float(self.model._p_drop) if (self.model.training and self.mode == N.MODE_DEFAULT) else 0.0
+
+    def _rebind_if_moved(self):
+        """The flat parameter buffer is re-created when the parameters move (``model.to()``,
+        ``load_state_dict(assign=True)``): follow it and drop every captured graph, which holds the old addresses.  The
+        AdamW moments keep their meaning (same layout)."""
+        flat, desc = self.model._runtime()
+        if self.model._fp.version == self._flat_version and flat.data_ptr() == self.flat.data_ptr():
+            return
+        if flat.device != self.device or flat.numel() != self.flat.numel():
+            raise RuntimeError("the model's parameters moved to another device or changed size under a FusedTrainer")
+        self.flat, self.desc, self._flat_version = flat, desc, self.model._fp.version
+        if self._frozen is not None:
+            self._snapshot = flat.clone()
+        self._ws = {k: v for k, v in self._ws.items() if not isinstance(v, dict)}       # keep plain buffers, drop graphs
+
     def _workspace(self, B, T, label_dtype, train):
         from ..models import fast as FM
-        key = (B, T, label_dtype, train, FM.get_head_backward() if train else None, FM.get_head_precision())   # a captured graph bakes the kernel choice in
+        # a captured graph bakes in the kernel choice AND every by-value launch argument that depends on host state: the
+        # dropout probability (model.train() / .eval()) and the gradient scale
+        p_drop = self._p_drop_now() if train else 0.0
+        key = (B, T, label_dtype, train, FM.get_head_backward() if train else None, FM.get_head_precision(),
+               p_drop, float(self.grad_scale) if train else None)
         ws = self._ws.get(key)
         if ws is not None:
             return ws
         d, dev, lib = self.desc, self.device, self.lib
         n_win = (T - d.window_len) // d.slide_step + 1
         n_terms = FM._TERMS[FM.get_head_precision()]
-        ws = dict(B=B, T=T, n_win=n_win, graph=None, fwd_terms=n_terms if (n_terms and lib.fastb200_head_tc_supported(d)) else 0,
+        ws = dict(B=B, T=T, n_win=n_win, graph=None, p_drop=p_drop, grad_scale=float(self.grad_scale), fwd_terms=n_terms if (n_terms and lib.fastb200_head_tc_supported(d)) else 0,
                   x=torch.empty(B, d.n_chan, T, device=dev),
                   y=torch.empty(B, device=dev, dtype=label_dtype),
                   feat=torch.empty(B, n_win, d.n_zones, d.dim_cnn, device=dev),
@@ -133,7 +155,7 @@ class FusedTrainer:
         lib, d, p = self.lib, self.desc, N.ptr
         st = N.stream_ptr(self.device)
         B, T, n_win = ws["B"], ws["T"], ws["n_win"]
-        p_drop = float(self.model._p_drop) if (self.model.training and self.mode == N.MODE_DEFAULT) else 0.0
+        p_drop = ws["p_drop"]
         N.check(lib.fastb200_head_pack(d, p(self.flat), p(self.packed), st), "head_pack")
         n_terms = ws["fwd_terms"]
         if n_terms:
@@ -152,7 +174,7 @@ class FusedTrainer:
         N.check(lib.fastb200_transformer_fwd(d, p(self.flat), p(ws["feat"]), B, n_win, self.mode, p_drop, self.seed, 0,
                                              p(self.step_dev), p(ws["logits"]), p(ws["tr_saved"]), st), "transformer_fwd")
         N.check(lib.fastb200_ce_fwd_bwd(p(ws["logits"]), p(ws["y"]), ws["y"].element_size(), B, d.n_classes,
-                                        self.grad_scale, p(self.loss), p(ws["dlogits"]), p(ws["pred"]), p(self.n_correct), st),
+                                        ws["grad_scale"], p(self.loss), p(ws["dlogits"]), p(ws["pred"]), p(self.n_correct), st),
                 "ce")
         self.grad.zero_()
         N.check(lib.fastb200_transformer_bwd(d, p(self.flat), p(ws["feat"]), p(ws["tr_saved"]), p(ws["dlogits"]), B, n_win,
@@ -215,6 +237,7 @@ class FusedTrainer:
             x = x.float()
         if y.dtype not in (torch.uint8, torch.int64):
             y = y.long()
+        self._rebind_if_moved()
         ws = self._workspace(x.shape[0], x.shape[2], y.dtype, train)
         phases = self._phases(ws, train)
         with torch.cuda.device(self.device):

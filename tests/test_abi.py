@@ -38,6 +38,17 @@ def test_library_exports_every_declared_symbol(libpath):
         assert hasattr(lib, name), f"{name} declared in fastb200.h but not exported"
 
 
+def test_library_exports_nothing_the_header_does_not_declare(libpath):
+    """exports (dynamic symbol table, defined `fastb200_*` functions) == header: no undeclared debug entry points ship."""
+    import subprocess
+    out = subprocess.run(["nm", "-D", "--defined-only", libpath], capture_output=True, text=True, check=True).stdout
+    exported = sorted({ln.split()[-1] for ln in out.splitlines() if ln.split() and ln.split()[-1].startswith("fastb200_")})
+    assert exported == _header_symbols()
+    blob = open(libpath, "rb").read()
+    for knob in (b"FASTB200_TC_DBG", b"FASTB200_WG_SWAP", b"FASTB200_DGRAD", b"FASTB200_TR_GROUP"):
+        assert knob not in blob, f"debug environment knob {knob.decode()} is compiled into the shipped library"
+
+
 def test_binding_covers_header_and_struct_mirror_matches(libpath):
     from fast import _native as N
     assert sorted(N.SIGNATURES) == _header_symbols()
@@ -57,6 +68,16 @@ def test_argument_validation_without_a_gpu(libpath):
     assert rc < 0 and b"uint8 or int64" in lib.fastb200_last_error()
     with pytest.raises(RuntimeError, match="uint8 or int64"):
         N.check(rc, "ce")
+    # the tensor-core backward validates like its siblings (B, windows inside the trial, item bound) before touching memory
+    d = N.ModelDesc()
+    d.dim_cnn, d.n_zones, d.window_len, d.n_chan, d.slide_step = 32, 1, 250, 4, 125
+    d.zone_size[0] = 4
+    rc = lib.fastb200_head_bwd_tc(d, None, None, None, None, 2, 300, 5, 125, None, None, None, None)
+    assert rc < 0 and b"windows run past" in lib.fastb200_last_error()
+    rc = lib.fastb200_head_bwd_tc(d, None, None, None, None, -1, 800, 5, 125, None, None, None, None)
+    assert rc < 0 and b"bad B" in lib.fastb200_last_error()
+    rc = lib.fastb200_head_bwd_tc(d, None, None, None, None, 2, 800, 5, 125, None, None, None, None)
+    assert rc < 0 and b"NULL buffer" in lib.fastb200_last_error()
 
 
 def test_fused_filter_support_predicate_is_host_logic(libpath):

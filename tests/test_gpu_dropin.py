@@ -222,3 +222,49 @@ def test_forward_backward_under_bf16_autocast(golden):
     with torch.autocast('cuda', dtype=torch.bfloat16), torch.no_grad():
         lb = m(x.cuda().bfloat16())
     assert lb.dtype == torch.float32 and rel_err(lb, golden["prod/logits"]) < 2e-2
+
+
+# ---------------------------------------------------------------------------------------------- FusedTrainer host state
+def test_fused_trainer_follows_mode_toggles_and_parameter_moves():
+    """A captured step graph bakes in by-value arguments and buffer addresses: toggling train()/eval(), changing grad_scale,
+    a stand-alone ``model.head(...)`` call or a parameter swap must never leave the trainer replaying stale state."""
+    from fast.models import FAST
+    from fast.train import FusedTrainer
+    torch.manual_seed(42)
+    m = FAST(make_prod_cfg(dropout=0.1)).cuda().eval()
+    ft = FusedTrainer(m, lr=5e-4, use_graph=True)
+    g = torch.Generator().manual_seed(2)
+    x = (torch.randn(8, 64, 800, generator=g) * 3).cuda()
+    y = torch.randint(0, 5, (8,), generator=g).to(torch.uint8).cuda()
+    for _ in range(2):
+        ft.train_step(x, y)                                          # eval mode: captured with p_drop = 0
+    m.train()
+    for _ in range(2):
+        ft.train_step(x, y)                                          # train mode: must be a different graph (p_drop = 0.1)
+    drops = sorted(w["p_drop"] for w in ft._ws.values() if isinstance(w, dict) and "dlogits" in w)
+    assert drops == [0.0, pytest.approx(0.1)]
+    ft.grad_scale = 0.5
+    ft.train_step(x, y)
+    assert sorted(w["grad_scale"] for w in ft._ws.values() if isinstance(w, dict) and "dlogits" in w) == [0.5, 1.0, 1.0]
+    ft.grad_scale = 1.0
+    # stand-alone Head call: adopts its slice of the owner's flat buffer instead of pulling the parameters out of it
+    ptr0, ver0 = ft.flat.data_ptr(), m._fp.version
+    with torch.no_grad():
+        f1 = m.head(x[:, :, :250].contiguous())
+        f2 = m.forward_head(x)[:, 0]
+    assert torch.equal(f1, f2)
+    assert m._runtime()[0].data_ptr() == ptr0 and m._fp.version == ver0
+    # swapping the Parameter objects (load_state_dict(assign=True)) re-creates the flat buffer: the trainer follows it
+    sd = {k: v.detach().clone() * 0.5 for k, v in m.state_dict().items()}
+    m.load_state_dict(sd, assign=True)
+    m.eval()
+    loss0, _, _ = ft.eval_step(x, y)
+    loss0 = float(loss0)
+    with torch.no_grad():
+        ref = float(torch.nn.CrossEntropyLoss()(m(x), y.long()))
+    assert abs(loss0 - ref) < 1e-5
+    assert ft.flat.data_ptr() == m._runtime()[0].data_ptr() != ptr0
+    m.train()
+    before = m.state_dict()["last_layer.weight"].clone()
+    ft.train_step(x, y)
+    assert not torch.equal(before, m.state_dict()["last_layer.weight"])          # the update landed in the LIVE parameters

@@ -1,4 +1,5 @@
-"""Dev check (GPU): tensor-core head vs FFMA head vs the CPU oracle; timing at batch 8192."""
+"""Dev check (GPU): tensor-core head vs FFMA head vs the CPU oracle; timing at batch 8192.
+Needs a developer build of the library: FASTB200_NVCC_EXTRA="-DFASTB200_PROFILE" python imagined-speech-decoding_b200/build.py --force"""
 import os, sys, types, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [os.path.join(ROOT, "imagined-speech-decoding_b200"), ROOT]
