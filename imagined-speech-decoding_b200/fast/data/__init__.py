@@ -15,6 +15,7 @@ from .preprocess import (
     load_test_set,
     load_test_set_per_subject,
     load_subject_train_val,
+    subject_train_val_device,
     trials_from_mat,
 )
 from .filters import bandpass_sos, sosfiltfilt, resample_poly, sosfiltfilt_resample, bandpass_resample, bandpass_resample_host
@@ -35,6 +36,7 @@ __all__ = [
     "NAME",
     "TARGET_TIMEPOINTS",
     "trials_from_mat",
+    "subject_train_val_device",
     "bandpass_sos",
     "sosfiltfilt",
     "resample_poly",

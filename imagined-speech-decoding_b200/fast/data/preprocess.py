@@ -4,6 +4,10 @@ Drop-in for the reference's ``src/fast/data/preprocess.py``: same constants (:19
 return types (:49-190, :197-224).  File parsing (``scipy.io.loadmat`` / ``h5py`` / ``pandas.read_excel``) stays stock
 Python; the array math behind it -- (T, C, N) MATLAB layout -> (N, C, 800) float32 with the last sample repeated
 (:57-62) -- runs as the ``fastb200_trials_from_mat`` kernel (include/fastb200.h) and there is no NumPy fallback for it.
+
+GPU-direct ingestion (additive): ``subject_train_val_device`` / ``_split_device`` keep the trials on the device (file ->
+pinned staging -> re-layout kernel -> optional band-pass / resample kernel -> CUDA tensor) for ``fast.train.cv``; the
+reference-named ``load_*`` functions are NumPy views of them.
 """
 import os
 
@@ -47,18 +51,44 @@ def _device(device=None):
     return torch.device(device)
 
 
-def trials_from_mat(x_tcn, target_len=TARGET_TIMEPOINTS, device=None):
-    """(T, C, N) float64/float32 array as ``loadmat`` returns it -> (N, C, target_len) float32 CUDA tensor,
-    right edge-padded: ``np.transpose(x,(2,1,0)).astype(float32)`` + ``np.pad(..., 'edge')`` (preprocess.py:60-62)."""
+_STAGE = {}      # device -> [pinned uint8 staging buffer, event recorded after the last copy out of it]
+
+
+def _to_device(x_np, device):
+    """Pageable NumPy array -> device tensor through a reusable PINNED staging buffer and one asynchronous copy
+    (``torch.from_numpy(x).to(device)`` on pageable memory is a synchronous, driver-staged copy).  The staging buffer is
+    reused by the next call only after its copy has completed (event), so callers never wait on the H2D themselves."""
+    x_np = np.ascontiguousarray(x_np)
+    slot = _STAGE.get(device)
+    if slot is None or slot[0].numel() < x_np.nbytes:
+        slot = [torch.empty(max(x_np.nbytes, 1 << 20), dtype=torch.uint8, pin_memory=True), None]
+        _STAGE[device] = slot
+    if slot[1] is not None:
+        slot[1].synchronize()
+    view = slot[0][:x_np.nbytes].view(torch.from_numpy(x_np).dtype).view(x_np.shape)
+    view.copy_(torch.from_numpy(x_np))
+    with torch.cuda.device(device):
+        out = view.to(device, non_blocking=True)
+        slot[1] = torch.cuda.Event()
+        slot[1].record(torch.cuda.current_stream(device))
+    return out
+
+
+def trials_from_mat(x_tcn, target_len=TARGET_TIMEPOINTS, device=None, pad=None):
+    """(T, C, N) float64/float32 array as ``loadmat`` returns it -> (N, C, T_pad) float32 CUDA tensor, right edge-padded:
+    ``np.transpose(x,(2,1,0)).astype(float32)`` + ``np.pad(..., 'edge')`` (preprocess.py:60-62) as ONE kernel over a
+    pinned-staged copy of the file's array.  ``pad=k`` appends exactly k samples (the train / validation loaders' fixed
+    ``(0, 5)``, preprocess.py:62,85,177,186,209); otherwise the trial is padded up to ``target_len`` (test-set rule,
+    preprocess.py:110-113)."""
     device = _device(device)
-    x = np.ascontiguousarray(x_tcn)
+    x = np.asarray(x_tcn)
     if x.ndim != 3:
         raise ValueError(f"expected a (T, C, N) array, got shape {x.shape}")
     if x.dtype not in (np.float32, np.float64):
         x = x.astype(np.float64)
     T, C, n = x.shape
-    T_pad = max(int(target_len), T)
-    src = torch.from_numpy(x).to(device, non_blocking=False)
+    T_pad = T + int(pad) if pad is not None else max(int(target_len), T)
+    src = _to_device(x, device)
     dst = torch.empty(n, C, T_pad, device=device, dtype=torch.float32)
     with torch.cuda.device(device):
         N.check(N.lib().fastb200_trials_from_mat(N.ptr(src), x.dtype.itemsize, N.ptr(dst), T, C, n, T_pad,
@@ -70,7 +100,7 @@ def _pad_edge_ncT(x_ncT, target_len, device=None):
     """(N, C, T) -> (N, C, target_len) float32, edge padded (test-set layout, preprocess.py:110-114).
     Same kernel: a (N, C, T) array is the (T', C', N') layout of its own transpose, so go through a device permute."""
     device = _device(device)
-    x = torch.from_numpy(np.ascontiguousarray(x_ncT)).to(device)
+    x = _to_device(x_ncT, device)
     tcn = x.permute(2, 1, 0).contiguous()
     if tcn.dtype not in (torch.float32, torch.float64):
         tcn = tcn.double()
@@ -87,12 +117,25 @@ def _labels_from_onehot(y):
     return np.asarray(y).argmax(0).astype(np.uint8)
 
 
-def _split(mat_path, key):
+def _split_device(mat_path, key, device=None, bandpass=None):
+    """One split of one subject, device resident: ``loadmat`` (stock parser) -> pinned staging -> fused transpose + cast +
+    edge-pad kernel (-> optional zero-phase band-pass / resample kernel) -> (X (n, C, T') float32 CUDA, Y (n,) uint8 CUDA).
+    Nothing comes back to the host.  ``bandpass``: None, or keyword arguments of ``fast.data.filters.bandpass_resample``."""
     import scipy.io
     data = scipy.io.loadmat(mat_path)
     x = np.asarray(data[key]['x'])[0][0]
     y = np.asarray(data[key]['y'])[0][0]
-    return trials_from_mat(x).cpu().numpy(), _labels_from_onehot(y)
+    X = trials_from_mat(x, device=device, pad=5)
+    if bandpass is not None:
+        from .filters import bandpass_resample
+        X = bandpass_resample(X, **dict(bandpass))
+    Y = torch.from_numpy(_labels_from_onehot(y)).to(X.device, non_blocking=True)
+    return X, Y
+
+
+def _split(mat_path, key):
+    X, Y = _split_device(mat_path, key)
+    return X.cpu().numpy(), Y.cpu().numpy()
 
 
 def _load_split_all(base_folder, folder_name, key, tag):
@@ -165,16 +208,28 @@ def load_test_set_per_subject(base_folder, excel_path):
     return test_data
 
 
-def load_subject_train_val(base_folder, SID):
-    """Train + validation trials of one subject, concatenated  (preprocess.py:164-190)."""
+def subject_train_val_device(base_folder, SID, device=None, bandpass=None):
+    """GPU-direct form of ``load_subject_train_val``: the subject's train + validation trials as CUDA
+    tensors (X (n, 64, 800) float32, Y (n,) uint8) that ``fast.train.cv.run_cv_jobs`` / ``train_fold`` consume in place --
+    file -> pinned staging -> one re-layout kernel per split (+ the band-pass / resample kernel when ``bandpass`` is
+    given) -> concatenation on the device; no host round trip of the trial data."""
     X_parts, Y_parts = [], []
     for folder_name, key in (('Training set', 'epo_train'), ('Validation set', 'epo_validation')):
         path = os.path.join(base_folder, folder_name, f'Data_Sample{SID}.mat')
         if os.path.exists(path):
-            x, y = _split(path, key)
+            x, y = _split_device(path, key, device=device, bandpass=bandpass)
             X_parts.append(x)
             Y_parts.append(y)
-    return np.concatenate(X_parts, axis=0), np.concatenate(Y_parts, axis=0)
+    if not X_parts:
+        raise ValueError("need at least one array to concatenate")          # np.concatenate's message on an empty list
+    return torch.cat(X_parts, dim=0), torch.cat(Y_parts, dim=0)
+
+
+def load_subject_train_val(base_folder, SID):
+    """Train + validation trials of one subject, concatenated  (preprocess.py:164-190).  NumPy view of
+    ``subject_train_val_device`` for the unchanged scripts."""
+    X, Y = subject_train_val_device(base_folder, SID)
+    return X.cpu().numpy(), Y.cpu().numpy()
 
 
 # ---------------------------------------------------------------------------------------------- HDF5 cache writer

@@ -268,3 +268,58 @@ def test_fused_trainer_follows_mode_toggles_and_parameter_moves():
     before = m.state_dict()["last_layer.weight"].clone()
     ft.train_step(x, y)
     assert not torch.equal(before, m.state_dict()["last_layer.weight"])          # the update landed in the LIVE parameters
+
+
+# ---------------------------------------------------------------------------------------------- GPU-direct ingestion (f3)
+def _fake_dataset(root, sid="01", n_train=12, n_val=4, seed=0):
+    """Two MATLAB v5 files in the competition's layout: struct epo_* with x (T, C, N) float64 and one-hot y (5, N)."""
+    import scipy.io
+    rng = np.random.default_rng(seed)
+    parts = {}
+    for folder, key, n in (("Training set", "epo_train", n_train), ("Validation set", "epo_validation", n_val)):
+        os.makedirs(os.path.join(root, folder), exist_ok=True)
+        x = rng.standard_normal((795, 64, n)) * 20.0 + rng.uniform(-50, 50, (1, 64, 1))
+        y = np.eye(5)[:, rng.integers(0, 5, n)]
+        scipy.io.savemat(os.path.join(root, folder, f"Data_Sample{sid}.mat"), {key: {"x": x, "y": y}})
+        parts[key] = (x, y)
+    return parts
+
+
+def test_gpu_direct_ingestion_matches_reference_loader_arithmetic(tmp_path):
+    from fast.data import load_subject_train_val, subject_train_val_device, load_training_set
+    from fast.train import cv as CV
+    parts = _fake_dataset(str(tmp_path))
+    # the reference's arithmetic (preprocess.py:170-190): transpose, float32, five edge samples, one-hot argmax, concatenate
+    ref_x, ref_y = [], []
+    for key in ("epo_train", "epo_validation"):
+        x, y = parts[key]
+        xr = np.pad(np.transpose(x, (2, 1, 0)).astype(np.float32), ((0, 0), (0, 0), (0, 5)), 'edge')
+        ref_x.append(xr); ref_y.append(y.argmax(0).astype(np.uint8))
+    ref_x, ref_y = np.concatenate(ref_x), np.concatenate(ref_y)
+    X, Y = load_subject_train_val(str(tmp_path), "01")
+    assert isinstance(X, np.ndarray) and X.dtype == np.float32 and Y.dtype == np.uint8
+    assert X.shape == (16, 64, 800) and np.array_equal(X, ref_x) and np.array_equal(Y, ref_y)
+    Xd, Yd = subject_train_val_device(str(tmp_path), "01")
+    assert Xd.is_cuda and Yd.is_cuda and Yd.dtype == torch.uint8
+    assert np.array_equal(Xd.cpu().numpy(), ref_x) and np.array_equal(Yd.cpu().numpy(), ref_y)
+    Xt, Yt = load_training_set(str(tmp_path))
+    assert np.array_equal(Xt, ref_x[:12]) and np.array_equal(Yt, ref_y[:12])
+    # fused band-pass + resample on the way in (north_star (c) feeding (a)): against scipy on the reference-layout array
+    from scipy import signal
+    Xf, _ = subject_train_val_device(str(tmp_path), "01", bandpass=dict(low=4.0, high=40.0, order=4, up=4, down=5))
+    sos = signal.butter(4, [4, 40], 'bandpass', fs=250, output='sos')
+    want = signal.resample_poly(signal.sosfiltfilt(sos, ref_x[:3].astype(np.float64), axis=-1), 4, 5, axis=-1)
+    assert Xf.shape == (16, 64, 640) and Xf.dtype == torch.float32
+    assert rel_err(Xf[:3], want) < 1e-5
+    # the CV runner consumes the device tensors in place (no host copy of the trials)
+    cfg = make_prod_cfg(dropout=0.0)
+    seen = []
+
+    def load(sid):
+        out = subject_train_val_device(str(tmp_path), sid)
+        seen.append(out[0].data_ptr())
+        return out
+
+    res = CV.run_cv_jobs(cfg, [(0, "01", 0)], load, str(tmp_path / "cv"), max_epochs=2, batch_size=8, n_folds=2, seed=3)
+    assert len(res) == 1 and len(seen) == 1 and np.isfinite(res[0]["best_val_acc"])
+    assert os.path.exists(tmp_path / "cv" / "sub-01" / "fold-0-best.pth")
