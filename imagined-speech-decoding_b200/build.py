@@ -12,8 +12,12 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
-LIB = os.path.join(HERE, "libfastb200.so")
-STAMP = os.path.join(HERE, "build", "libfastb200.stamp")
+# FASTB200_BUILD_DIR: developer builds of kernel variants go to their own directory (library + objects) and leave the
+# shipped in-tree library alone
+_OUT = os.environ.get("FASTB200_BUILD_DIR")
+LIB = os.path.join(_OUT, "libfastb200.so") if _OUT else os.path.join(HERE, "libfastb200.so")
+OBJ_DIR = os.path.join(_OUT, "build") if _OUT else os.path.join(HERE, "build")
+STAMP = os.path.join(OBJ_DIR, "libfastb200.stamp")
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -49,11 +53,11 @@ def build(force=False, verbose=False):
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     if not os.path.exists(nvcc):
         raise RuntimeError(f"nvcc not found at {nvcc}; libfastb200.so must be prebuilt in-tree")
-    os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
+    os.makedirs(OBJ_DIR, exist_ok=True)
     objs = []
     procs = []
     for src in sources():
-        obj = os.path.join(HERE, "build", os.path.basename(src)[:-3] + ".o")
+        obj = os.path.join(OBJ_DIR, os.path.basename(src)[:-3] + ".o")
         cmd = [nvcc, *NVCC_FLAGS, "-c", src, "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")

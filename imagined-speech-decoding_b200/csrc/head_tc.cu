@@ -374,7 +374,24 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
         const float* beff = reinterpret_cast<const float*>(wz + (EMB_CHUNKS + 2 * CONV_CHUNKS) * LB) + CW * h;
         const bool live = t < a.T_out;                              // rows past the window are the next conv's zero padding
         const bool own = live && (s == 0 ? t < a.split : t >= a.split);
-        mbar_wait(&sm.w_full, 0);                                   // beff visible
+        // Waits of the stream's 8 epilogue warps: ONE warp polls the mbarrier, the other seven park in a named hardware
+        // barrier.  A polling warp re-issues ~7 instructions every ~30 cycles; with all 16 epilogue warps spinning (ncu, round 2:
+        // 3,000 SYNCS + 1,500 NANOSLEEP of the 20,900 instructions per item, and every SYNCS is a shared-memory wavefront
+        // competing with the MMA operand fetch) the spinners took as many issue slots as the warps doing the epilogue
+        // arithmetic they were waiting for.  The pollers sit on sub-partitions 2 / 3, away from the two MMA issuers.
+        const bool poller = (warp & 7) == 2 + s;
+        auto group_wait = [&](uint64_t* bar, uint32_t parity) {
+#ifndef FB_NO_GROUP_WAIT
+            if (poller) mbar_wait(bar, parity);
+            asm volatile("bar.sync %0, 256;" ::"r"(1 + s) : "memory");
+#else
+            mbar_wait(bar, parity);
+#endif
+        };
+        group_wait(&sm.w_full, 0);                                  // beff visible
+        float be[CW];                                               // this warp's 16 collapsed-bias values: registers, not 16 LDS per item
+#pragma unroll
+        for (int i = 0; i < CW; ++i) be[i] = beff[i];
         long long ew = 0, ep[5] = {0, 0, 0, 0, 0};
 
         // accumulator (NT column groups) -> v[CW]
@@ -400,7 +417,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
             const size_t item = (size_t)(rank + it * nz) * a.Z + z;
             float* dst = a.saved + (item * 3 + stage) * (size_t)(F * a.TS) + (size_t)(CW * h) * a.TS + t;
 #pragma unroll
-            for (int i = 0; i < CW; ++i) dst[(size_t)i * a.TS] = add_bias ? v[i] + beff[i] : v[i];
+            for (int i = 0; i < CW; ++i) dst[(size_t)i * a.TS] = add_bias ? v[i] + be[i] : v[i];
         };
         auto to_operand = [&](float (&v)[CW], bool add_bias, int it, uint64_t* ready) {
             uint8_t* yt = yt0 + (it & 1) * y_bytes(NT);
@@ -411,7 +428,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
 #pragma unroll
                 for (int e = 0; e < 8; ++e) {
                     float val = v[8 * j + e];
-                    if (add_bias) val += beff[8 * j + e];
+                    if (add_bias) val += be[8 * j + e];
                     x8[e] = live ? val : 0.f;
                 }
                 uint4 o[NT];
@@ -426,7 +443,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
         auto epi_embed = [&](int it) {
             long long c0 = 0;
             if (PROF) c0 = clock64();
-            mbar_wait(&sm.de_full[s], it & 1);
+            group_wait(&sm.de_full[s], it & 1);
             if (PROF) ew += clock64() - c0;
             tc_fence_after();
             float v[CW];
@@ -438,7 +455,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
         auto epi_cnn3 = [&](int it) {
             long long c0 = 0;
             if (PROF) c0 = clock64();
-            mbar_wait(&sm.dm_full[s], 0);                           // two completions per item: cnn3 = even, cnn4 = odd
+            group_wait(&sm.dm_full[s], 0);                          // two completions per item: cnn3 = even, cnn4 = odd
             if (PROF) ew += clock64() - c0;
             tc_fence_after();
             float v[CW];
@@ -450,7 +467,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
         auto epi_cnn4 = [&](int it) {
             long long c0 = 0, c1 = 0;
             if (PROF) c0 = clock64();
-            mbar_wait(&sm.dm_full[s], 1);
+            group_wait(&sm.dm_full[s], 1);
             if (PROF) { c1 = clock64(); ew += c1 - c0; }
             tc_fence_after();
             float v[CW];
@@ -479,7 +496,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
             const int par = it & 1;
             // the two streams have independent issuers and may drift apart: do not touch the slot of item `it` before the
             // feature of item it - 2 (same slot) has been written
-            if (it >= 2) mbar_wait(&sm.red_free[par], ((it >> 1) - 1) & 1);
+            if (it >= 2) group_wait(&sm.red_free[par], ((it >> 1) - 1) & 1);
             if ((lane & 1) == 0) sm.red[par][warp][lane >> 1] = v[0];
             __syncwarp();
             int old = 0;

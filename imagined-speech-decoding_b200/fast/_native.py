@@ -11,7 +11,8 @@ import os
 import torch
 
 _PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(_PKG, "libfastb200.so")
+# FASTB200_LIB: developer override (A/B timing of kernel variants built elsewhere); the default is the in-tree library
+LIB_PATH = os.environ.get("FASTB200_LIB") or os.path.join(_PKG, "libfastb200.so")
 
 MAX_ZONES, MAX_CHANS, MAX_LAYERS = 16, 256, 16
 MODE_DEFAULT, MODE_TRAIN_HEAD = 0, 1
@@ -47,6 +48,7 @@ SIGNATURES = {
     "fastb200_version": (C.c_int, []),
     "fastb200_sizeof_model": (C.c_int, []),
     "fastb200_last_error": (C.c_char_p, []),
+    "fastb200_launch_count": (C.c_int64, []),
     "fastb200_window_gather": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
     "fastb200_head_packed_floats": (C.c_int64, [_MP]),
     "fastb200_head_saved_floats": (C.c_int64, [_MP, C.c_int, C.c_int]),
@@ -104,6 +106,20 @@ def lib():
             raise RuntimeError("fastb200_model layout mismatch between include/fastb200.h and fast/_native.py")
         _lib = handle
     return _lib
+
+
+_replayed = 0      # launches replayed from captured CUDA graphs (they do not pass through the library)
+
+
+def note_replayed(n: int):
+    global _replayed
+    _replayed += int(n)
+
+
+def launch_count() -> int:
+    """Kernels of libfastb200.so launched by this process so far: direct launches (counted inside the library) plus the
+    launches of every CUDA-graph replay the Python side reported with ``note_replayed``."""
+    return int(lib().fastb200_launch_count()) + _replayed
 
 
 def check(code: int, what: str):

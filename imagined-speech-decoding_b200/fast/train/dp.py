@@ -103,3 +103,48 @@ class DataParallelTrainer(FusedTrainer):
         t = torch.stack([self.loss[0].double() / self.world, self.n_correct[0].double()])
         dist.all_reduce(t, group=self.group)
         return float(t[0]), int(t[1])
+
+
+def dp_selfcheck(config, reduce="p2p", steps=4, per_rank=2, group=None, seed=77):
+    """Run inside an initialised process group (one rank per GPU): ``steps`` data-parallel steps on a synthetic global batch
+    of ``per_rank * world`` trials, then check (1) every replica's flat parameter buffer is BIT-identical to rank 0's and
+    (2) rank 0's losses / parameters equal a single-GPU ``FusedTrainer`` run on the concatenated batch.  Returns a dict
+    (same on every rank) -- the evidence bench.py / smoke() print for the exchange path (``fastb200_adamw_flat_peers`` for
+    ``reduce='p2p'``, one ``ncclAllReduce`` for ``'nccl'``)."""
+    from ..models import FAST
+    group = group if group is not None else dist.group.WORLD
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    n = per_rank * world
+    C, T = len(config.electrodes), config.seq_len
+    factors = [1.0, 0.5, 0.25, 1.0] * ((steps + 3) // 4)
+    torch.manual_seed(100 + rank)                               # different initial replicas: the broadcast must fix that
+    model = FAST(config).to(dev).train()
+    ft = DataParallelTrainer(model, group=group, reduce=reduce, lr=5e-4, lr_factors=factors[:steps], use_graph=True, seed=1)
+    g = torch.Generator().manual_seed(seed)
+    batches = [(torch.randn(n, C, T, generator=g), torch.randint(0, config.n_classes, (n,), generator=g).to(torch.uint8))
+               for _ in range(steps)]
+    sl = shard_batch(n, rank, world)
+    losses = []
+    for x, y in batches:
+        ft.train_step(x[sl].to(dev), y[sl].to(dev))
+        losses.append(ft.global_loss_and_correct()[0])
+    flats = [torch.empty_like(ft.flat) for _ in range(world)]
+    dist.all_gather(flats, ft.flat.contiguous(), group=group)
+    identical = all(torch.equal(flats[0], f) for f in flats[1:])
+    out = torch.zeros(3, device=dev, dtype=torch.float64)
+    if rank == 0:
+        torch.manual_seed(100)
+        ref_model = FAST(config).to(dev).train()
+        ref = FusedTrainer(ref_model, lr=5e-4, lr_factors=factors[:steps], use_graph=False, seed=1)
+        ref_losses = [float(ref.train_step(x.to(dev), y.to(dev))[0]) for x, y in batches]
+        worst_loss = max(abs(a - b) / max(abs(b), 1e-12) for a, b in zip(losses, ref_losses))
+        # Adam turns rounding noise into +-lr steps where the true gradient is ~0 (e.g. the key third of in_proj_bias): compare
+        # the parameter buffers in the max norm relative to the largest parameter
+        worst_param = float((ft.flat - ref.flat).abs().max() / ref.flat.abs().max())
+        out = torch.tensor([worst_loss, worst_param, 1.0], device=dev, dtype=torch.float64)
+    dist.broadcast(out, src=dist.get_global_rank(group, 0), group=group)
+    return {"reduce": reduce if world > 1 else "none", "world": world, "steps": steps, "global_batch": n,
+            "replicas_bit_identical": bool(identical), "loss_rel_err_vs_single_gpu": float(out[0]),
+            "param_rel_err_vs_single_gpu": float(out[1]),
+            "ok": bool(identical and float(out[0]) < 1e-4 and float(out[1]) < 2e-3)}

@@ -260,11 +260,17 @@ class FusedTrainer:
                         continue
                     g = torch.cuda.CUDAGraph()
                     side.wait_stream(torch.cuda.current_stream(self.device))
+                    c0 = self.lib.fastb200_launch_count()
                     with torch.cuda.stream(side):
                         with torch.cuda.graph(g, stream=side):
                             fn()
                     torch.cuda.current_stream(self.device).wait_stream(side)
-                    replay.append(g.replay)
+                    n_launch = self.lib.fastb200_launch_count() - c0       # kernels recorded into this graph
+
+                    def replay_fn(g=g, n_launch=n_launch):
+                        g.replay()
+                        N.note_replayed(n_launch)
+                    replay.append(replay_fn)
                 ws["graph"] = replay
             else:
                 for fn in ws["graph"]:

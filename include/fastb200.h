@@ -74,6 +74,9 @@ typedef struct fastb200_model {
 int         fastb200_version(void);
 int         fastb200_sizeof_model(void);      /* sizeof(fastb200_model): lets a binding verify its struct mirror */
 const char* fastb200_last_error(void);
+/* Number of kernel launches this process has issued through the library so far (a launch recorded into a CUDA graph
+ * under stream capture counts once, its replays do not pass through the library).  New: measurement aid for bench.py. */
+int64_t     fastb200_launch_count(void);
 
 /* ---- index kernels: window unfold + zone gather -------------------------------------------------------- */
 /*

@@ -59,12 +59,15 @@ def test_alternative_heads_inside_fast_vs_reference(alt, head, no_tf32):
     loss = torch.nn.CrossEntropyLoss()(logits, y)
     loss.backward()
     assert rel_err(logits, alt[f"{head}/train_logits"]) < TOL
-    assert abs(float(loss) - float(alt[f"{head}/loss"])) < 1e-5
+    assert abs(float(loss.detach()) - float(alt[f"{head}/loss"])) < 1e-5
+    gmax = max(float(np.abs(alt[f"{head}/grad/{k}"]).max()) for k, _ in m.named_parameters())
     for k, p in m.named_parameters():
         ref = alt[f"{head}/grad/{k}"]
         assert p.grad is not None, k
-        if np.abs(ref).max() < 1e-7:        # conv weights/biases directly in front of a BatchNorm: the true gradient is 0
-            assert float(p.grad.abs().max()) < 1e-5, k
+        if np.abs(ref).max() < 1e-4 * gmax:
+            # scale / shift directly in front of another BatchNorm (and conv weights in front of one): the true gradient is 0
+            # and both sides hold rounding noise (~1e-7): compare absolutely against the largest gradient of the model
+            assert float((p.grad.cpu() - torch.from_numpy(ref)).abs().max()) < 1e-5 * gmax, k
         else:
             # cuDNN's BatchNorm / conv backward reassociates; 5e-4 of the tensor's max on these stock composites
             assert rel_err(p.grad, ref) < 5e-4, (k, rel_err(p.grad, ref))

@@ -71,6 +71,47 @@ def test_train_fold_matches_oracle_loop_and_keeps_best_epoch():
         assert rel_err(t, best[k]) < 2e-3, k                    # a few AdamW steps: compare loosely, exactness is tested elsewhere
 
 
+def test_concurrent_folds_equal_folds_run_alone(tmp_path):
+    """``train_folds`` (one epoch graph with a parallel branch per fold) gives every fold the result it has when trained
+    alone -- production config (tensor-core kernels), three folds of one subject sharing x -- and ``run_cv_jobs(concurrent=3)``
+    writes the same artefacts as the sequential runner."""
+    from conftest import make_prod_cfg
+    from fast.train.cv import cv_jobs, kfold_indices, run_cv_jobs, train_fold, train_folds
+    cfg = make_prod_cfg()
+    g = torch.Generator().manual_seed(4)
+    x = torch.randn(36, 64, 800, generator=g)
+    y = (torch.arange(36) % 5).to(torch.uint8)
+    x[:, 3, :] += (y.float() - 2.0)[:, None]
+    xd, yd = x.cuda(), y.cuda()
+    folds = kfold_indices(36, 3, True, 1)
+    epochs, bs = 4, 16
+    alone = [train_fold(cfg, xd, yd, tr, va, max_epochs=epochs, batch_size=bs, seed=20 + k) for k, (tr, va) in enumerate(folds)]
+    both = train_folds(cfg, [dict(x=xd, y=yd, train_idx=tr, val_idx=va, seed=20 + k) for k, (tr, va) in enumerate(folds)],
+                       max_epochs=epochs, batch_size=bs)
+    assert len(both) == 3
+    for a, b in zip(alone, both):
+        # same arithmetic, same dropout / shuffle streams; only the order of the fp32 atomics inside the weight-gradient
+        # kernels differs from run to run
+        np.testing.assert_allclose(b["history"]["loss"], a["history"]["loss"], rtol=2e-3)
+        np.testing.assert_allclose(b["history"]["val_loss"], a["history"]["val_loss"], rtol=2e-3)
+        assert np.abs(np.array(b["history"]["val_acc"]) - np.array(a["history"]["val_acc"])).max() <= 1.0 / 12 + 1e-9
+        assert b["steps"] == a["steps"] == epochs * 2
+        for k in a["state_dict"]:
+            assert b["state_dict"][k].shape == a["state_dict"][k].shape
+    # the runner: concurrent groups leave the same files as one-at-a-time
+    data = {"01": (x, y)}
+    jobs = cv_jobs(["01"], 3)
+    d1 = run_cv_jobs(cfg, jobs, lambda s: data[s], str(tmp_path / "seq"), max_epochs=2, batch_size=bs, seed=3, n_folds=3)
+    d3 = run_cv_jobs(cfg, jobs, lambda s: data[s], str(tmp_path / "par"), max_epochs=2, batch_size=bs, seed=3, n_folds=3, concurrent=3)
+    assert [r["fold"] for r in d3] == [r["fold"] for r in d1] == [0, 1, 2]
+    for k in range(3):
+        for name in (f"fold-{k}-best.pth", f"fold-{k}_history.csv", f"fold-{k}_result.json"):
+            assert (tmp_path / "par" / "sub-01" / name).exists()
+        h1 = np.loadtxt(tmp_path / "seq" / "sub-01" / f"fold-{k}_history.csv", delimiter=",", skiprows=1)
+        h3 = np.loadtxt(tmp_path / "par" / "sub-01" / f"fold-{k}_history.csv", delimiter=",", skiprows=1)
+        np.testing.assert_allclose(h3[:, 1], h1[:, 1], rtol=2e-3)
+
+
 def test_run_cv_jobs_artifacts_resume_and_finalize(tmp_path):
     from fast.train.cv import cv_jobs, finalize_cv, run_cv_jobs, shard_jobs
     cfg = make_small_cfg()
