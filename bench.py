@@ -183,6 +183,28 @@ def launches():
     return N.launch_count()
 
 
+# The contract is ONE JSON line on stdout.  NCCL (banner under NCCL_DEBUG=VERSION/INFO) and other native libraries write to
+# file descriptor 1 directly, so for the B200 arm fd 1 is pointed at stderr for the whole run and the line goes to the saved
+# descriptor.
+_JSON_FD = None
+
+
+def capture_stdout():
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 # ------------------------------------------------------------------------------------------------ CPU arm (oracle port)
 def cpu_forward_trials_per_s(n_trials, chunk, repeats, threads):
     """The oracle port of the reference forward on the host cores: eval-mode logits for `n_trials` synthetic trials."""
@@ -911,7 +933,7 @@ def run_all(args, ctx):
         for k in ("stress_p2p", "stress_nccl"):
             if k in extra:
                 extra[k]["cpu_baseline"] = dict(cpu_t, sample=cpu_t["sample"] + " (production seq_len 800; a 4000-sample trial costs ~6.2x per trial)")
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_single(args, ctx):
@@ -946,7 +968,7 @@ def run_single(args, ctx):
             line["cpu_baseline"] = cpu_train_trials_per_s(64, threads)
         elif w == "preprocess":
             line["cpu_baseline"] = cpu_preprocess_baseline()
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
@@ -976,6 +998,7 @@ def main():
     if args.impl == "reference":
         run_reference(args, rank)
         return
+    capture_stdout()
     ctx = Ctx()
     if args.workload == "all":
         run_all(args, ctx)

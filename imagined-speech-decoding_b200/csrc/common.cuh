@@ -109,10 +109,17 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     #pragma unroll 1
     for (uint32_t spin = 0; spin < (1u << 24); ++spin) {
         // the suspend-time hint (ns) lets the hardware park the warp instead of re-issuing the poll
+#if FB_MBAR_SUSPEND_NS > 0
         asm volatile("{\n\t.reg .pred p;\n\t"
                      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
                      "selp.u32 %0, 1, 0, p;\n\t}"
                      : "=r"(done) : "r"(smem_u32(bar)), "r"(parity), "r"(FB_MBAR_SUSPEND_NS) : "memory");
+#else
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+#endif
         if (done) return;
     }
     __trap();

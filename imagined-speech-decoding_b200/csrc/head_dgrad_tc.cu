@@ -216,8 +216,16 @@ __global__ void __launch_bounds__(THREADS, 1) head_dgrad_tc_kernel(const __grid_
 #pragma unroll 1
         for (int it = 0; it < n_it; ++it) {
             const int slot = it % STG;
+#ifndef FB_NO_GROUP_WAIT_DG
+            if (half == 0) {                                        // one poller per stream, its partner parks in a named barrier (see head_tc.cu)
+                mbar_wait(&sm.stg_full[s][slot], (it / STG) & 1);
+                if (it >= 2) mbar_wait(&sm.tile_free[s][it & 1], ((it >> 1) - 1) & 1);
+            }
+            asm volatile("bar.sync %0, 64;" ::"r"(3 + s) : "memory");
+#else
             mbar_wait(&sm.stg_full[s][slot], (it / STG) & 1);
             if (it >= 2) mbar_wait(&sm.tile_free[s][it & 1], ((it >> 1) - 1) & 1);
+#endif
             const float* sg = reinterpret_cast<const float*>(stg + (size_t)(s * STG + slot) * STG_BYTES);
             const float* df = sg + F * SR;
             const size_t item = (size_t)(rank + it * nz) * a.Z + z;
@@ -259,6 +267,16 @@ __global__ void __launch_bounds__(THREADS, 1) head_dgrad_tc_kernel(const __grid_
         uint8_t* yt0 = ys + 2 * s * y_bytes(NT) + (m + 2) * 16 + 2 * h * (RY * 16);
         const bool live = t < a.T_out;
         const bool own = live && (s == 0 ? t < a.split : t >= a.split);
+        // one polling warp per stream; the other seven epilogue warps park in a named hardware barrier (head_tc.cu explains why)
+        const bool poller = (warp & 7) == 2 + s;
+        auto group_wait = [&](uint64_t* bar, uint32_t parity) {
+#ifndef FB_NO_GROUP_WAIT_DG
+            if (poller) mbar_wait(bar, parity);
+            asm volatile("bar.sync %0, 256;" ::"r"(1 + s) : "memory");
+#else
+            mbar_wait(bar, parity);
+#endif
+        };
         auto drain = [&](float (&v)[CW]) {
             float u[NT - 1][CW];
             tmem_ld16(lane_addr, v);
@@ -283,7 +301,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_dgrad_tc_kernel(const __grid_
 #pragma unroll 1
         for (int it = 0; it < n_it; ++it) {
             // ---- dL/dy3: drain -> masked -> operand tile of this parity (overwrites dL/dy4, already consumed) + global
-            mbar_wait(&sm.dm_full[s], 0);
+            group_wait(&sm.dm_full[s], 0);
             tc_fence_after();
             float v[CW];
             drain(v);
@@ -305,7 +323,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_dgrad_tc_kernel(const __grid_
             }
             save_rows(v, it, 1);
             // ---- dL/dy2: drain -> global
-            mbar_wait(&sm.dm_full[s], 1);
+            group_wait(&sm.dm_full[s], 1);
             tc_fence_after();
             drain(v);
             tc_fence_before();

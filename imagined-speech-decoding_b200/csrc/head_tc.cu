@@ -342,8 +342,16 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
 #pragma unroll 1
             for (int it = 0; it < n_it; ++it) {
                 const int slot = it % STG;
+#if !defined(FB_NO_GROUP_WAIT) && !defined(FB_NO_CONV_GROUP_WAIT)
+                if (half == 0) {                                    // one poller per stream, its partner parks in a named barrier
+                    mbar_wait(&sm.stg_full[s][slot], (it / STG) & 1);
+                    if (it > 0) mbar_wait(&sm.x_empty[s], (it - 1) & 1);
+                }
+                asm volatile("bar.sync %0, 64;" ::"r"(3 + s) : "memory");
+#else
                 mbar_wait(&sm.stg_full[s][slot], (it / STG) & 1);
                 if (it > 0) mbar_wait(&sm.x_empty[s], (it - 1) & 1);
+#endif
                 const float* sg = stg + slot * (STG_BYTES / 4);
                 for (int j = 0; j < n_xchunk; ++j)
 #pragma unroll
@@ -389,9 +397,15 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
 #endif
         };
         group_wait(&sm.w_full, 0);                                  // beff visible
-        float be[CW];                                               // this warp's 16 collapsed-bias values: registers, not 16 LDS per item
+        // this warp's 16 collapsed-bias values live in registers for NT = 2 (16 shared-memory loads per thread and item on the
+        // critical path between the TMEM drain and the operand-tile store otherwise: -16 % kernel time, round 2)
+#if defined(FB_BEFF_SMEM)
+        const float* be = beff;
+#else
+        float be[CW];
 #pragma unroll
         for (int i = 0; i < CW; ++i) be[i] = beff[i];
+#endif
         long long ew = 0, ep[5] = {0, 0, 0, 0, 0};
 
         // accumulator (NT column groups) -> v[CW]

@@ -180,11 +180,27 @@ __global__ void __launch_bounds__(THREADS, 1) head_wgrad_tc_kernel(const __grid_
                     asm volatile("bar.sync 1, %0;" ::"n"(CONV_WARPS * 32) : "memory");        // ... and everybody's; all are done with item it - 1
                     if (it + 1 < n_it) gather(it + 1);                                        // tile (it + 1) & 1 was last read for item it - 1
                 }
+                // one polling warp (warp 2), the other seven converter warps park in named barrier 2: eight warps spinning on
+                // an mbarrier take the issue slots and shared-memory cycles the converting warps need (see head_tc.cu)
+#ifndef FB_NO_GROUP_WAIT_WG
+                if (it >= 2) {
+                    if (warp == 2) mbar_wait(&sm.tile_empty[buf], ((it >> 1) - 1) & 1);
+                    asm volatile("bar.sync 2, %0;" ::"n"(CONV_WARPS * 32) : "memory");
+                }
+#else
                 if (it >= 2) mbar_wait(&sm.tile_empty[buf], ((it >> 1) - 1) & 1);
+#endif
 #pragma unroll 1
                 for (int half = 0; half < 2; ++half) {
                     const int L = 2 * it + half, slot = L & 1;
+#ifndef FB_NO_GROUP_WAIT_WG
+                    if (!(emb && half == 0)) {
+                        if (warp == 2) mbar_wait(&sm.stg_full[slot], (L >> 1) & 1);
+                        asm volatile("bar.sync 2, %0;" ::"n"(CONV_WARPS * 32) : "memory");
+                    }
+#else
                     if (!(emb && half == 0)) mbar_wait(&sm.stg_full[slot], (L >> 1) & 1);
+#endif
                     const float* sg = (emb && half == 0) ? reinterpret_cast<const float*>(stg) + (it & 1) * 16 * TSX
                                                          : reinterpret_cast<const float*>(stg + (size_t)slot * slot_bytes);
                     if (emb && half == 0) {

@@ -49,6 +49,7 @@ SIGNATURES = {
     "fastb200_sizeof_model": (C.c_int, []),
     "fastb200_last_error": (C.c_char_p, []),
     "fastb200_launch_count": (C.c_int64, []),
+    "fastb200_copy_rows_async": (C.c_int, [_P, C.c_int64, _P, C.c_int64, C.c_int64, C.c_int64, _P]),
     "fastb200_window_gather": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
     "fastb200_head_packed_floats": (C.c_int64, [_MP]),
     "fastb200_head_saved_floats": (C.c_int64, [_MP, C.c_int, C.c_int]),

@@ -77,6 +77,11 @@ const char* fastb200_last_error(void);
 /* Number of kernel launches this process has issued through the library so far (a launch recorded into a CUDA graph
  * under stream capture counts once, its replays do not pass through the library).  New: measurement aid for bench.py. */
 int64_t     fastb200_launch_count(void);
+/* Row-strided async copy (host<->device, one cudaMemcpy2DAsync on `stream`): `rows` rows of `width_bytes`, pitches in bytes.
+ * Used by FAST.predict to upload only the samples the windows read (replaces the full-row x.cuda() of
+ * inference_on_loader, src/fast/train/trainer.py:89).  Pointers may be pinned host or device memory. */
+int         fastb200_copy_rows_async(void* dst, int64_t dst_pitch, const void* src, int64_t src_pitch, int64_t width_bytes,
+                                     int64_t rows, void* stream);
 
 /* ---- index kernels: window unfold + zone gather -------------------------------------------------------- */
 /*

@@ -326,3 +326,23 @@ def test_gpu_direct_ingestion_matches_reference_loader_arithmetic(tmp_path):
     res = CV.run_cv_jobs(cfg, [(0, "01", 0)], load, str(tmp_path / "cv"), max_epochs=2, batch_size=8, n_folds=2, seed=3)
     assert len(res) == 1 and len(seen) == 1 and np.isfinite(res[0]["best_val_acc"])
     assert os.path.exists(tmp_path / "cv" / "sub-01" / "fold-0-best.pth")
+
+
+# ---------------------------------------------------------------------------------------------- end-to-end predict (row-strided upload)
+def test_predict_from_pinned_host_ships_only_the_samples_read():
+    from fast.models import FAST
+    torch.manual_seed(42)
+    m = FAST(make_prod_cfg()).cuda().eval()
+    g = torch.Generator().manual_seed(6)
+    x = torch.randn(70, 64, 795, generator=g) * 30
+    want = m.predict(x.cuda())
+    xp = x.pin_memory()
+    got = m.predict(xp, chunk=32)                                    # 32 + 32 + 6: ragged tail, two staging buffers reused
+    assert torch.equal(got, want)
+    assert m._last_h2d_bytes == 70 * 64 * 750 * 4                    # 750 of the 795 samples per row (windows end at 500 + 250)
+    assert torch.equal(m.predict(x, chunk=32), want)                 # pageable host memory: plain full-row copies, same result
+    assert m._last_h2d_bytes == 70 * 64 * 795 * 4
+    x800 = torch.nn.functional.pad(x, (0, 5), mode="replicate").pin_memory()
+    assert torch.equal(m.predict(x800, chunk=64), want)              # the reference's 800-sample layout: same logits
+    assert m._last_h2d_bytes == 70 * 64 * 750 * 4
+    assert m.predict(xp[:0]).shape == (0,)
