@@ -177,9 +177,15 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
             mbar_init(&sm.x_empty[s], 1);
             mbar_init(&sm.de_full[s], 1);
             mbar_init(&sm.dm_full[s], 1);
+#ifndef FB_THREAD_ARRIVE
+            mbar_init(&sm.ye_ready[s], EPI_WARPS / 2);           // one arrival per epilogue warp of the stream (lane 0, after __syncwarp)
+            mbar_init(&sm.yc_ready[s], EPI_WARPS / 2);
+            mbar_init(&sm.d_free[s], EPI_WARPS / 2);
+#else
             mbar_init(&sm.ye_ready[s], EPI_WARPS * 16);
             mbar_init(&sm.yc_ready[s], EPI_WARPS * 16);
             mbar_init(&sm.d_free[s], EPI_WARPS * 16);
+#endif
         }
         mbar_init(&sm.red_free[0], 1);
         mbar_init(&sm.red_free[1], 1);
@@ -399,13 +405,14 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
         group_wait(&sm.w_full, 0);                                  // beff visible
         // this warp's 16 collapsed-bias values live in registers for NT = 2 (16 shared-memory loads per thread and item on the
         // critical path between the TMEM drain and the operand-tile store otherwise: -16 % kernel time, round 2)
-#if defined(FB_BEFF_SMEM)
-        const float* be = beff;
-#else
-        float be[CW];
+        // (NT = 3 keeps them in shared memory: its drain holds 48 accumulator values and the extra 16 registers cost more
+        // than the loads -- 10.23 vs 10.39 ms per 8192 trials.)
+        float be_reg[NT == 2 ? CW : 1];
+        if (NT == 2) {
 #pragma unroll
-        for (int i = 0; i < CW; ++i) be[i] = beff[i];
-#endif
+            for (int i = 0; i < CW; ++i) be_reg[NT == 2 ? i : 0] = beff[i];
+        }
+        const float* be = NT == 2 ? be_reg : beff;
         long long ew = 0, ep[5] = {0, 0, 0, 0, 0};
 
         // accumulator (NT column groups) -> v[CW]
@@ -452,7 +459,12 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
             }
             fence_proxy_async();
             tc_fence_before();
+#ifndef FB_THREAD_ARRIVE
+            __syncwarp();                                           // every lane's stores are fenced; one arrival per warp
+            if (lane == 0) mbar_arrive(ready);
+#else
             mbar_arrive(ready);
+#endif
         };
         auto epi_embed = [&](int it) {
             long long c0 = 0;
@@ -487,7 +499,12 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
             float v[CW];
             drain(lane_addr + s * DCOLS, v);
             tc_fence_before();
+#ifndef FB_THREAD_ARRIVE
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm.d_free[s]);              // accumulator drained: next item's cnn3 may overwrite it
+#else
             mbar_arrive(&sm.d_free[s]);                             // accumulator drained: next item's cnn3 may overwrite it
+#endif
             if (SAVE) save_rows(v, false, it, 2);
 #pragma unroll
             for (int i = 0; i < CW; i += 2) {
