@@ -134,7 +134,8 @@ struct FwdArgs {
 
 struct Smem {                                  // fixed part at the start of dynamic shared memory
     uint64_t w_full;
-    uint64_t x_full[2], x_empty[2], de_full[2], dm_full[2], ye_ready[2], yc_ready[2], d_free[2];
+    uint64_t x_full[2], x_empty[2], de_full[2], ye_ready[2], yc_ready[2], d_free[2];
+    uint64_t dm_full[2][2];                    // per stream, per conv layer (cnn3, cnn4): one completion per item each
     uint64_t stg_full[2][2], stg_empty[2][2];
     uint64_t red_free[2];                      // partial-sum slot of item parity p may be reused (its feature was written)
     uint32_t tmem_base;
@@ -176,16 +177,13 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
             for (int i = 0; i < 2; ++i) { mbar_init(&sm.stg_full[s][i], 32); mbar_init(&sm.stg_empty[s][i], 64); }
             mbar_init(&sm.x_empty[s], 1);
             mbar_init(&sm.de_full[s], 1);
-            mbar_init(&sm.dm_full[s], 1);
-#ifndef FB_THREAD_ARRIVE
-            mbar_init(&sm.ye_ready[s], EPI_WARPS / 2);           // one arrival per epilogue warp of the stream (lane 0, after __syncwarp)
-            mbar_init(&sm.yc_ready[s], EPI_WARPS / 2);
-            mbar_init(&sm.d_free[s], EPI_WARPS / 2);
-#else
+            mbar_init(&sm.dm_full[s][0], 1);
+            mbar_init(&sm.dm_full[s][1], 1);
+            // every epilogue thread arrives for itself, as soon as ITS stores are fenced: one arrival per warp behind a
+            // __syncwarp was measured 9 % slower (the operand hand-over sits on the critical path of the stream)
             mbar_init(&sm.ye_ready[s], EPI_WARPS * 16);
             mbar_init(&sm.yc_ready[s], EPI_WARPS * 16);
             mbar_init(&sm.d_free[s], EPI_WARPS * 16);
-#endif
         }
         mbar_init(&sm.red_free[0], 1);
         mbar_init(&sm.red_free[1], 1);
@@ -290,7 +288,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
                              idesc_bf16(32 * (NT - t)), acc);
                         acc = 1;
                     }
-            umma_commit(&sm.dm_full[s]);
+            umma_commit(&sm.dm_full[s][layer]);
         };
         issue_embed(0);
         for (int it = 0; it < n_it; ++it) {
@@ -459,12 +457,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
             }
             fence_proxy_async();
             tc_fence_before();
-#ifndef FB_THREAD_ARRIVE
-            __syncwarp();                                           // every lane's stores are fenced; one arrival per warp
-            if (lane == 0) mbar_arrive(ready);
-#else
             mbar_arrive(ready);
-#endif
         };
         auto epi_embed = [&](int it) {
             long long c0 = 0;
@@ -481,7 +474,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
         auto epi_cnn3 = [&](int it) {
             long long c0 = 0;
             if (PROF) c0 = clock64();
-            group_wait(&sm.dm_full[s], 0);                          // two completions per item: cnn3 = even, cnn4 = odd
+            group_wait(&sm.dm_full[s][0], it & 1);
             if (PROF) ew += clock64() - c0;
             tc_fence_after();
             float v[CW];
@@ -493,18 +486,13 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
         auto epi_cnn4 = [&](int it) {
             long long c0 = 0, c1 = 0;
             if (PROF) c0 = clock64();
-            group_wait(&sm.dm_full[s], 1);
+            group_wait(&sm.dm_full[s][1], it & 1);
             if (PROF) { c1 = clock64(); ew += c1 - c0; }
             tc_fence_after();
             float v[CW];
             drain(lane_addr + s * DCOLS, v);
             tc_fence_before();
-#ifndef FB_THREAD_ARRIVE
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&sm.d_free[s]);              // accumulator drained: next item's cnn3 may overwrite it
-#else
             mbar_arrive(&sm.d_free[s]);                             // accumulator drained: next item's cnn3 may overwrite it
-#endif
             if (SAVE) save_rows(v, false, it, 2);
 #pragma unroll
             for (int i = 0; i < CW; i += 2) {
@@ -525,9 +513,12 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
             }
             v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
             const int par = it & 1;
+            long long c2 = 0;
+            if (PROF) { c2 = clock64(); ep[3] += c2 - c1; }         // drain + GELU + row reduction
             // the two streams have independent issuers and may drift apart: do not touch the slot of item `it` before the
             // feature of item it - 2 (same slot) has been written
             if (it >= 2) group_wait(&sm.red_free[par], ((it >> 1) - 1) & 1);
+            if (PROF) ep[4] += clock64() - c2;                      // wait for the partial-sum slot
             if ((lane & 1) == 0) sm.red[par][warp][lane >> 1] = v[0];
             __syncwarp();
             int old = 0;
@@ -559,7 +550,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
             if (it + 1 < n_it) epi_embed(it + 1);
             epi_cnn4(it);
         }
-        if (PROF && tid == 0) { long long* o = a.prof + (size_t)blockIdx.x * 16; o[6] = ew; o[8] = ep[0]; o[9] = ep[1]; o[10] = ep[2]; }
+        if (PROF && tid == 0) { long long* o = a.prof + (size_t)blockIdx.x * 16; o[6] = ew; o[8] = ep[0]; o[9] = ep[1]; o[10] = ep[2]; o[11] = ep[3]; o[12] = ep[4]; }
         if (PROF && tid == 256) a.prof[(size_t)blockIdx.x * 16 + 7] = ew;
     }
     tc_fence_before();
