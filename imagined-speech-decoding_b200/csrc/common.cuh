@@ -62,8 +62,9 @@ int head_dgrad_launch(const fastb200_model* m, const float* packed, const float*
 // Tensor-core input-gradient chain (head_dgrad_tc.cu): writes dL/dy4, dL/dy3, dL/dy2 to dys; fpacked = head_pack output.
 int head_dgrad_tc_supported(const fastb200_model* m);
 int64_t head_dgrad_tc_packed_bytes(const fastb200_model* m, int n_terms);
+// write_dy4 = 0: dL/dy4 is not written (head_wgrad_tc recomputes it from the saved y4 and dfeat in its converter).
 int head_dgrad_tc_launch(const fastb200_model* m, const float* fpacked, const float* saved, const float* dfeat, int B,
-                         int n_win, float* dys, void* packed_ws, int n_terms, void* stream);
+                         int n_win, float* dys, void* packed_ws, int n_terms, int write_dy4, void* stream);
 
 // ---- device helpers -------------------------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {

@@ -60,25 +60,12 @@ __global__ void head_pack_dgrad_tc_kernel(fastb200_model m, const float* __restr
     }
 }
 
-// d/dx [x Phi(x)] = Phi(x) + x phi(x), with Phi from the same A&S 7.1.26 erfc as the forward's fused GELU (|error| <= 1.5e-7)
-__device__ __forceinline__ float gelu_grad_fast(float x) {
-    const float ax = fabsf(x);
-    const float t = rcp_approx(fmaf(ax, 0.3275911f * 0.70710678118654752440f, 1.0f));
-    float q = fmaf(t, 0.5f * 1.061405429f, 0.5f * -1.453152027f);
-    q = fmaf(t, q, 0.5f * 1.421413741f);
-    q = fmaf(t, q, 0.5f * -0.284496736f);
-    q = fmaf(t, q, 0.5f * 0.254829592f);
-    const float e = ex2_approx(x * x * -0.72134752044448170368f);       // exp(-x^2 / 2)
-    const float h = q * t * e;                                          // 0.5 erfc(|x| / sqrt 2)
-    const float cdf = x >= 0.f ? 1.0f - h : h;
-    return fmaf(x * 0.39894228040143267794f, e, cdf);
-}
-
 struct Args {
     const uint8_t* packed;                     // head_pack_dgrad_tc_kernel output
     const float* saved;                        // per item 3 x [F][TS]: y2, y3, y4
     const float* dfeat;                        // (B, n_win, Z, F)
     float* dys;                                // per item 3 x [F][TS]: dL/dy4, dL/dy3, dL/dy2 (written)
+    int write_dy4;                             // 0: dL/dy4 stays on chip (the weight-gradient kernel recomputes it from y4)
     int BN, Z, TS;
     int T_out, split, tb1;
     uint8_t cta_zone[NUM_SMS], cta_rank[NUM_SMS], zone_ctas[FASTB200_MAX_ZONES];
@@ -245,7 +232,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_dgrad_tc_kernel(const __grid_
                     const float g = df[8 * j + e] * inv_T * gelu_grad_fast(y);
                     v[e] = live ? g : 0.f;
                 }
-                if (own) {
+                if (own && a.write_dy4) {
 #pragma unroll
                     for (int e = 0; e < 8; ++e) dy4[(size_t)(8 * j + e) * a.TS + t] = v[e];
                 }
@@ -350,14 +337,14 @@ int fb::head_dgrad_tc_supported(const fastb200_model* m) {
 int64_t fb::head_dgrad_tc_packed_bytes(const fastb200_model* m, int n_terms) { return (int64_t)m->n_zones * dg::zone_bytes(n_terms); }
 
 int fb::head_dgrad_tc_launch(const fastb200_model* m, const float* fpacked, const float* saved, const float* dfeat, int B,
-                             int n_win, float* dys, void* packed_ws, int n_terms, void* stream) {
+                             int n_win, float* dys, void* packed_ws, int n_terms, int write_dy4, void* stream) {
     FB_REQUIRE(head_dgrad_tc_supported(m), "shape not supported by the tensor-core input-gradient kernel");
     FB_REQUIRE(n_terms == 2 || n_terms == 3, "n_terms must be 2 or 3");
     FB_REQUIRE((int64_t)B * n_win < (1ll << 31) / FASTB200_MAX_ZONES, "too many items for one launch");
     dg::head_pack_dgrad_tc_kernel<<<dim3(m->n_zones, 8), 256, 0, as_stream(stream)>>>(*m, fpacked, static_cast<uint8_t*>(packed_ws), n_terms);
     if (int r = check_launch("head_pack_dgrad_tc")) return r;
     dg::Args a;
-    a.packed = static_cast<const uint8_t*>(packed_ws); a.saved = saved; a.dfeat = dfeat; a.dys = dys;
+    a.packed = static_cast<const uint8_t*>(packed_ws); a.saved = saved; a.dfeat = dfeat; a.dys = dys; a.write_dy4 = write_dy4;
     a.BN = B * n_win; a.Z = m->n_zones; a.TS = head_saved_stride(m->window_len);
     a.T_out = m->window_len - 4; a.split = a.T_out / 2; a.tb1 = a.T_out - 128;
     const int Z = m->n_zones;

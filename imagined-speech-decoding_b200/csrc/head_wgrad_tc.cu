@@ -56,6 +56,8 @@ struct Args {
     const float* saved;                        // per item 3 x [F][TS]: y2, y3, y4 (head_fwd)
     const float* dys;                          // per item 3 x [F][TS]: dL/dy4, dL/dy3, dL/dy2 (head_dgrad_kernel)
     const float* x;                            // (B, C, T) trials: A operand of the collapsed-embed layer (layer 2)
+    const float* dfeat;                        // (B, n_win, Z, F): with dy4_from_y4, dL/dy4 = dfeat / T_out * gelu'(y4) is formed in the converter
+    int dy4_from_y4;                           // 1: the cnn4 layer's B operand is recomputed from the saved y4 (dL/dy4 never went to HBM)
     float* gpacked;
     int BN, Z, TS, T_out, ksteps;
     int n_win, step, C, T, W;
@@ -123,10 +125,14 @@ __global__ void __launch_bounds__(THREADS, 1) head_wgrad_tc_kernel(const __grid_
                     const int slot = L & 1, it = L >> 1;
                     if (L >= 2) mbar_wait(&sm.stg_empty[slot], ((L >> 1) - 1) & 1);
                     const size_t item = (size_t)(rank + it * nc) * a.Z + z;
+                    const bool recompute = slot == 1 && layer == 1 && a.dy4_from_y4;
                     const float* src = slot == 0 ? a.saved + item * 3 * item_sz + (size_t)layer * item_sz              // y2 / y3
+                                     : recompute ? a.saved + item * 3 * item_sz + 2 * item_sz                          // y4 (-> dy4 in the converter)
                                                  : a.dys + item * 3 * item_sz + (size_t)(emb ? 2 : 1 - layer) * item_sz;   // dy3 / dy4 / dy2
-                    mbar_expect_tx(&sm.stg_full[slot], tensor_bytes);
+                    mbar_expect_tx(&sm.stg_full[slot], tensor_bytes + (recompute ? (uint32_t)(F * 4) : 0u));
                     bulk_g2s(stg + (size_t)slot * slot_bytes, src, tensor_bytes, &sm.stg_full[slot]);
+                    // the item's dfeat row rides behind the tensor in the slot's spare bytes (slot_bytes - tensor_bytes = 512)
+                    if (recompute) bulk_g2s(stg + (size_t)slot * slot_bytes + tensor_bytes, a.dfeat + item * F, F * 4, &sm.stg_full[slot]);
                 }
             }
             __syncwarp();
@@ -220,12 +226,19 @@ __global__ void __launch_bounds__(THREADS, 1) head_wgrad_tc_kernel(const __grid_
                         }
                     } else {
                         uint8_t* tile = tiles + buf * 2 * TILE + half * TILE + (half == 0 ? 2 * 16 : 0);     // A rows are shifted by the 2 pad rows
+                        const bool recompute = half == 1 && layer == 1 && a.dy4_from_y4;
+                        const float* df = sg + F * a.TS;                                  // dfeat row behind the staged tensor
+                        const float inv_T = 1.0f / (float)a.T_out;
                         for (int t = ct; t < a.T_out; t += CONV_WARPS * 32) {
 #pragma unroll
                             for (int p = 0; p < 4; ++p) {
                                 float v[8];
 #pragma unroll
                                 for (int e = 0; e < 8; ++e) v[e] = sg[(8 * p + e) * a.TS + t];
+                                if (recompute) {                    // same expression as head_dgrad_tc's first stage: bit-identical dL/dy4
+#pragma unroll
+                                    for (int e = 0; e < 8; ++e) v[e] = df[8 * p + e] * inv_T * gelu_grad_fast(v[e]);
+                                }
                                 if (emb) {
 #pragma unroll
                                     for (int e = 0; e < 8; ++e) bs[p][e] += v[e];
@@ -317,7 +330,7 @@ extern "C" int fastb200_head_bwd_tc(const fastb200_model* m, const float* packed
     // every zone fits the 16-channel electrode tile; otherwise the CUDA-core kernel keeps them (and dx)
     bool embed_tc = dx == nullptr;
     for (int z = 0; z < m->n_zones; ++z) embed_tc = embed_tc && m->zone_size[z] <= 16;
-    int dg_terms = 2;
+    int dg_terms = 2, dy4_from_y4 = 0;
     bool dg_ffma = false;
 #ifdef FASTB200_DEBUG
     if (const char* dg_env = getenv("FASTB200_DGRAD")) {                              // developer builds: "ffma" forces the CUDA-core chain, "3" = 3 terms
@@ -327,10 +340,13 @@ extern "C" int fastb200_head_bwd_tc(const fastb200_model* m, const float* packed
 #endif
     if (embed_tc && head_dgrad_tc_supported(m) && !dg_ffma) {
         float* pk = work + (int64_t)B * n_win * m->n_zones * 3 * m->dim_cnn * head_saved_stride(m->window_len);
-        if (int r = head_dgrad_tc_launch(m, packed, saved, dfeat, B, n_win, work, pk, dg_terms, stream)) return r;
+#ifndef FB_WRITE_DY4
+        dy4_from_y4 = 1;        // dL/dy4 is element-wise in y4: the weight-gradient kernel re-forms it, the 1.3 GB per 1024 trials stay off HBM
+#endif
+        if (int r = head_dgrad_tc_launch(m, packed, saved, dfeat, B, n_win, work, pk, dg_terms, /*write_dy4=*/!dy4_from_y4, stream)) return r;
     } else if (int r = head_dgrad_launch(m, packed, x, saved, dfeat, B, T, n_win, step, gpacked, dx, work, embed_tc ? 1 : 0, stream)) return r;
     wg::Args a;
-    a.saved = saved; a.dys = work; a.gpacked = gpacked; a.x = x;
+    a.saved = saved; a.dys = work; a.gpacked = gpacked; a.x = x; a.dfeat = dfeat; a.dy4_from_y4 = dy4_from_y4;
     a.BN = B * n_win; a.Z = m->n_zones; a.TS = head_saved_stride(m->window_len); a.T_out = m->window_len - 4;
     a.ksteps = ceil_div(a.T_out, 16);
     a.n_win = n_win; a.step = step; a.C = m->n_chan; a.T = T; a.W = m->window_len;
