@@ -666,7 +666,7 @@ def measure_cv(args, ctx):
     subjects = SUBJECTS[:args.subjects]
     jobs = CV.cv_jobs(subjects, 5)
     J = max(1, args.cv_concurrent)
-    mine = CV.shard_jobs(jobs, rank, world)
+    mine = CV.shard_jobs_contiguous(jobs, rank, world)      # subject-major blocks: a rank loads ~15 / N subjects, not one per job
     save = args.cv_dir or os.path.join(tempfile.gettempdir(), "fastb200_cv")
     if rank == 0:
         shutil.rmtree(save, ignore_errors=True)

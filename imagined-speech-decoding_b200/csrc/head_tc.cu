@@ -343,15 +343,20 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
             const int s = (warp - CONV_WARP0) >> 1, half = (warp - CONV_WARP0) & 1;
             const float* stg = reinterpret_cast<const float*>(ys + 4 * y_bytes(NT)) + s * STG * (STG_BYTES / 4);
             uint8_t* xt = xs + s * x_bytes(NT);
+            long long cw[3] = {0, 0, 0};
 #pragma unroll 1
             for (int it = 0; it < n_it; ++it) {
                 const int slot = it % STG;
+                long long q0 = 0, q1 = 0, q2 = 0;
+                if (PROF) q0 = clock64();
 #if !defined(FB_NO_GROUP_WAIT) && !defined(FB_NO_CONV_GROUP_WAIT)
                 if (half == 0) {                                    // one poller per stream, its partner parks in a named barrier
                     mbar_wait(&sm.stg_full[s][slot], (it / STG) & 1);
+                    if (PROF) q1 = clock64();
                     if (it > 0) mbar_wait(&sm.x_empty[s], (it - 1) & 1);
                 }
                 asm volatile("bar.sync %0, 64;" ::"r"(3 + s) : "memory");
+                if (PROF) { q2 = clock64(); cw[0] += q1 - q0; cw[1] += q2 - q1; }
 #else
                 mbar_wait(&sm.stg_full[s][slot], (it / STG) & 1);
                 if (it > 0) mbar_wait(&sm.x_empty[s], (it - 1) & 1);
@@ -374,6 +379,11 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
                 fence_proxy_async();
                 mbar_arrive(&sm.x_full[s]);
                 mbar_arrive(&sm.stg_empty[s][slot]);
+                if (PROF) cw[2] += clock64() - q2;
+            }
+            if (PROF && warp == CONV_WARP0 && lane == 0) {
+                long long* o = a.prof + (size_t)blockIdx.x * 16;
+                o[13] = cw[0]; o[14] = cw[1]; o[15] = cw[2];
             }
         }
     } else {

@@ -67,6 +67,18 @@ def shard_jobs(jobs, rank: int, world: int):
     return list(jobs[rank::world])
 
 
+def shard_jobs_contiguous(jobs, rank: int, world: int):
+    """Balanced CONTIGUOUS partition of the subject-major job list: rank r takes jobs [r n / g, (r + 1) n / g), sizes differing
+    by at most one (the same ceil(75 / g) rounds as ``shard_jobs``).  A rank then touches ~n_subjects / g subjects instead of
+    min(n_jobs / g, n_subjects): each subject is read from disk and uploaded by one or two ranks only, and the concurrent
+    groups of ``run_cv_jobs(concurrent=J)`` are the folds of ONE subject sharing its resident trials."""
+    if not 0 <= rank < world:
+        raise ValueError(f"rank {rank} outside world {world}")
+    n = len(jobs)
+    lo, hi = (rank * n) // world, ((rank + 1) * n) // world
+    return list(jobs[lo:hi])
+
+
 class JobQueue:
     """Dynamic alternative to ``shard_jobs``: an atomic counter in the torch.distributed key-value store hands out job
     indices, so a rank that finishes early takes the next job (no collective, works before/without NCCL)."""

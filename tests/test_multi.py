@@ -90,6 +90,20 @@ def test_job_partition_and_selection_rules():
     assert abs(macro_f1(yt, yp) - f1_score(yt, yp, average="macro")) < 1e-12
 
 
+def test_contiguous_shards_are_balanced_disjoint_and_subject_local():
+    from fast.train.cv import cv_jobs, shard_jobs_contiguous
+    jobs = cv_jobs([f"{i:02d}" for i in range(1, 16)], 5)
+    for world in (1, 2, 3, 4, 8, 75, 80):
+        parts = [shard_jobs_contiguous(jobs, r, world) for r in range(world)]
+        assert sum(parts, []) == jobs                                   # disjoint, complete, order preserved
+        sizes = [len(p) for p in parts]
+        assert max(sizes) - min(sizes) <= 1 and max(sizes) == -(-75 // world)
+        if world <= 8:
+            assert max(len({sid for _, sid, _ in p}) for p in parts) <= -(-15 // world) + 1
+    with pytest.raises(ValueError):
+        shard_jobs_contiguous(jobs, 3, 3)
+
+
 def test_synthetic_subject_is_balanced_and_seeded():
     from fast.train.cv import synthetic_subject
     (X, Y), (Xt, Yt) = synthetic_subject(3, n_trials=35, n_test=10, n_chan=4, n_samples=16)
