@@ -750,6 +750,30 @@ static int set_smem(K kernel, size_t bytes) {
 
 using namespace fb;
 
+// Shared-memory footprints of the CUDA-core kernels (the window is resident in shared memory): the same expressions the
+// launchers below use, so the support predicate and the launch can never disagree.
+static size_t head_fwd_smem_floats(const fastb200_model& m) {
+    const int F = m.dim_cnn, RS = head_row_stride(m.window_len), n_tt = head_n_tt(m.window_len), mcz = max_cz(m);
+    int fl = 2 * F * RS + 2 * F * TAPS * F + round_up(F, 4) + round_up(n_tt * F, 4) + 4;
+    const int need_alias = mcz * RS + round_up(mcz * TAPS * F, 4);
+    if (need_alias > F * RS) fl += need_alias;
+    return (size_t)fl;
+}
+static size_t head_bwd_smem_floats(const fastb200_model& m) {
+    const int F = m.dim_cnn, RS = head_n_tt(m.window_len) * 128 + 36;
+    return (size_t)((2 * F + 32) * RS + 2 * F * TAPS * F + round_up(F, 4) + 4);
+}
+
+// 1 when the fused Conv4Layers kernels cover this head shape (dim_cnn 8 / 16 / 32, zones of 1..32 electrodes, a window that
+// fits the shared-memory resident CUDA-core kernels -- about 1,600 samples forward, 550 backward at dim_cnn 32), else 0.  The
+// Python drop-in runs shapes outside it (e.g. Conv4Layers(dim=64), reference tests/test_model.py:278-284) as stock torch ops.
+extern "C" int fastb200_head_supported(const fastb200_model* m, int need_backward) {
+    if (validate_model(m)) return 0;
+    if (head_fwd_smem_floats(*m) * sizeof(float) > 227 * 1024) return 0;
+    if (need_backward && head_bwd_smem_floats(*m) * sizeof(float) > 227 * 1024) return 0;
+    return 1;
+}
+
 extern "C" int64_t fastb200_head_packed_floats(const fastb200_model* m) {
     if (validate_model(m)) return -1;
     return packed_zone(*m, m->n_zones - 1).end;

@@ -51,6 +51,7 @@ SIGNATURES = {
     "fastb200_launch_count": (C.c_int64, []),
     "fastb200_copy_rows_async": (C.c_int, [_P, C.c_int64, _P, C.c_int64, C.c_int64, C.c_int64, _P]),
     "fastb200_window_gather": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
+    "fastb200_head_supported": (C.c_int, [_MP, C.c_int]),
     "fastb200_head_packed_floats": (C.c_int64, [_MP]),
     "fastb200_head_saved_floats": (C.c_int64, [_MP, C.c_int, C.c_int]),
     "fastb200_head_pack": (C.c_int, [_MP, _P, _P, _P]),

@@ -336,6 +336,43 @@ class _TransformerFn(torch.autograd.Function):
 
 
 # ------------------------------------------------------------------------------------------------------------------
+# shapes outside the fused kernels: stock torch CUDA ops (the reference's own op sequence), never a CPU path
+# ------------------------------------------------------------------------------------------------------------------
+_FUSED_OK_CACHE = {}
+
+
+def _fused_head_ok(window_len, zone_sizes, dim_cnn, need_backward) -> bool:
+    """Do the fused Conv4Layers kernels cover this head shape?  (``fastb200_head_supported``: dim_cnn 8/16/32, zones of
+    1..32 electrodes, window resident in shared memory.)  The reference accepts any dim / length
+    (fast.py:103-119; tests/test_model.py:270-284 use dim 64 and 500-sample windows), so the rest runs as torch ops."""
+    key = (int(window_len), tuple(int(z) for z in zone_sizes), int(dim_cnn), bool(need_backward))
+    ok = _FUSED_OK_CACHE.get(key)
+    if ok is None:
+        sizes = key[1]
+        ok = (0 < len(sizes) <= N.MAX_ZONES and sum(sizes) <= N.MAX_CHANS)
+        if ok:
+            d = N.ModelDesc()
+            d.window_len, d.n_zones, d.dim_cnn = key[0], len(sizes), key[2]
+            off = 0
+            for i, z in enumerate(sizes):
+                d.zone_size[i], d.zone_off[i] = z, off
+                off += z
+            ok = bool(N.lib().fastb200_head_supported(d, int(need_backward)))
+        _FUSED_OK_CACHE[key] = ok
+    return ok
+
+
+def _conv4_torch(enc, x):
+    """``Conv4Layers.forward`` (fast.py:111-119) as stock torch CUDA ops: x (R, Cz, T) -> (R, dim)."""
+    N.require_cuda(x, "input")
+    y = F.conv2d(x.unsqueeze(1), enc.cnn1.weight, enc.cnn1.bias)
+    y = F.conv2d(y, enc.cnn2.weight)
+    y = F.conv2d(y, enc.cnn3.weight, padding=(0, 2))
+    y = F.conv2d(y, enc.cnn4.weight, padding=(0, 2))
+    return F.gelu(y).mean(dim=(2, 3))
+
+
+# ------------------------------------------------------------------------------------------------------------------
 # modules (names, constructor order and parameter shapes follow the reference -> identical RNG use and state_dict)
 # ------------------------------------------------------------------------------------------------------------------
 class AttentionBlock(nn.Module):
@@ -377,6 +414,8 @@ class Conv4Layers(nn.Module):
 
     def forward(self, x):
         """x (R, Cz, T) -> (R, dim); the whole trial is one window and the zone is every row of x."""
+        if not _fused_head_ok(x.shape[2], [self._channels], self._dim, torch.is_grad_enabled()):
+            return _conv4_torch(self, x)
         if self._fp is None:
             self._fp = _FlatParams(self)
         flat = self._fp.ensure()
@@ -498,11 +537,20 @@ class Head(nn.Module):
     def _zone_index(self):
         return [self.index_dict[a].tolist() for a in self.encoders.keys()]
 
+    def fused_ok(self, window_len, need_backward=False) -> bool:
+        """True when this head runs as the fused kernels for windows of ``window_len`` samples."""
+        return self._fused and _fused_head_ok(window_len, [len(v) for v in self.index_dict.values()], self._feature_dim,
+                                              need_backward)
+
     def forward(self, x):
         """x (R, C, T) -> (R, Z, F)."""
         if not self._fused:
             N.require_cuda(x, "input")
             return torch.stack([enc(x[:, self.index_dict[a].to(x.device)]) for a, enc in self.encoders.items()], dim=1)
+        if not self.fused_ok(x.shape[2], torch.is_grad_enabled()):
+            N.require_cuda(x, "input")
+            return torch.stack([_conv4_torch(enc, x[:, self.index_dict[a].to(x.device)]) for a, enc in self.encoders.items()],
+                               dim=1)
         if self._fp is None:
             self._fp = _FlatParams(self)
         flat = self._fp.ensure()
@@ -563,7 +611,7 @@ class FAST(nn.Module):
             cfg, off = self.config, self._fp.offset
             d = N.ModelDesc()
             areas = list(self.head.encoders.keys())
-            if self.head._fused:
+            if self.head.fused_ok(cfg.window_len):
                 _head_desc(d, len(cfg.electrodes), cfg.window_len, cfg.slide_step, self.head._zone_index(),
                            cfg.dim_cnn, off, [f"head.encoders.{a}." for a in areas])
             else:
@@ -599,7 +647,7 @@ class FAST(nn.Module):
     def forward_head(self, x, step_override=None):
         """(B, C, T) -> (B, N, Z, F).  Window unfold, zone gather and the eight Conv4Layers stacks are one kernel."""
         step = self.config.slide_step if step_override is None else step_override
-        if not self.head._fused:
+        if not self.head.fused_ok(self.config.window_len, torch.is_grad_enabled()):
             N.require_cuda(x, "input")
             xw = x.unfold(-1, self.config.window_len, step)
             B, C, n, T = xw.shape
@@ -672,7 +720,7 @@ class FAST(nn.Module):
             C_, T = x.shape[1], x.shape[2]
             W_, S_ = self.config.window_len, self.config.slide_step
             T_used = ((T - W_) // S_) * S_ + W_ if T >= W_ else T
-            strided = (T_used < T and x.dtype == torch.float32 and x.is_contiguous() and x.is_pinned() and self.head._fused)
+            strided = (T_used < T and x.dtype == torch.float32 and x.is_contiguous() and x.is_pinned() and self.head.fused_ok(W_))
             T_dev = T_used if strided else T
             key = (chunk, C_, T_dev, dev)
             st = getattr(self, "_stage", None)

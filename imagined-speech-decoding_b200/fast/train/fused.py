@@ -37,8 +37,9 @@ class FusedTrainer:
 
     def __init__(self, model, lr=5e-4, lr_factors=None, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01,
                  forward_mode='default', use_graph=True, seed=None):
-        if not model.head._fused:
-            raise RuntimeError("FusedTrainer drives the fused Conv4Layers head only")
+        if not model.head.fused_ok(model.config.window_len, True):
+            raise RuntimeError("FusedTrainer drives the fused Conv4Layers head only (dim_cnn 8/16/32, zones of <= 32 electrodes, "
+                               "windows that fit the kernels); train other shapes through the nn.Module / autograd path")
         if forward_mode not in ('default', 'train_head', 'train_transformer'):
             raise NotImplementedError(forward_mode)
         self.model = model

@@ -94,6 +94,10 @@ int fastb200_window_gather(const float* x, const int32_t* chan, float* out,
                            int B, int C, int T, int W, int S, int n_win, int n_sel, void* stream);
 
 /* ---- zone embedding head (Conv4Layers x Z) -------------------------------------------------------------- */
+/* 1 when the fused Conv4Layers kernels cover this head shape (dim_cnn 8/16/32, zones of 1..32 electrodes, window resident in
+ * shared memory; need_backward also checks the backward kernel's footprint), else 0: the Python drop-in then runs the head
+ * as stock torch CUDA ops (reference Conv4Layers accepts any dim / length, src/fast/models/fast.py:103-119). */
+int         fastb200_head_supported(const fastb200_model* m, int need_backward);
 /* Size in floats of the packed head weights / packed head gradients for this model. */
 int64_t fastb200_head_packed_floats(const fastb200_model* m);
 /* Size in floats of the activations head_fwd saves for head_bwd: B*n_win*Z items x 3 x F x roundup4(W-4). */

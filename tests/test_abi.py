@@ -80,6 +80,18 @@ def test_argument_validation_without_a_gpu(libpath):
     assert rc < 0 and b"NULL buffer" in lib.fastb200_last_error()
 
 
+def test_head_support_predicate_is_host_logic(libpath):
+    """Which Conv4Layers shapes the fused kernels cover (the rest runs as stock torch CUDA ops in the drop-in)."""
+    from fast.models.fast import _fused_head_ok
+    assert _fused_head_ok(250, [6, 9, 6, 7, 7, 10, 15, 4], 32, True)          # production
+    assert _fused_head_ok(250, [4, 2, 2], 16, True) and _fused_head_ok(250, [1], 8, True)
+    assert not _fused_head_ok(250, [4], 64, False)                              # reference test_model.py:278-284 uses dim 64
+    assert not _fused_head_ok(250, [33], 32, False)                             # zone larger than the kernels' electrode tile
+    assert _fused_head_ok(500, [4], 32, False) and not _fused_head_ok(500, [4], 32, True)      # backward keeps more rows resident
+    assert not _fused_head_ok(4000, [4], 32, False)
+    assert not _fused_head_ok(250, [2] * 17, 32, False)                         # more zones than FASTB200_MAX_ZONES
+
+
 def test_fused_filter_support_predicate_is_host_logic(libpath):
     """fastb200_sosfiltfilt_resample_supported runs no kernel: the 250 -> 200 Hz chain with scipy's default FIR and padlen is
     the fused kernel's shape; another ratio, FIR alignment, a padlen shorter than the resampler's edge reach, or a row no
