@@ -64,8 +64,8 @@ struct Args {
     const uint8_t* packed;                     // head_pack_dgrad_tc_kernel output
     const float* saved;                        // per item 3 x [F][TS]: y2, y3, y4
     const float* dfeat;                        // (B, n_win, Z, F)
-    float* dys;                                // per item 3 x [F][TS]: dL/dy4, dL/dy3, dL/dy2 (written)
-    int write_dy4;                             // 0: dL/dy4 stays on chip (the weight-gradient kernel recomputes it from y4)
+    float* dys;                                // per item 3 slots of F * TS floats: split-bf16 operand images of dL/dy4, dL/dy3, dL/dy2 (written)
+    int write_dy4;                             // 0: no dL/dy4 image (a weight-gradient kernel that re-forms it from y4 follows)
     int BN, Z, TS;
     int T_out, split, tb1;
     uint8_t cta_zone[NUM_SMS], cta_rank[NUM_SMS], zone_ctas[FASTB200_MAX_ZONES];
@@ -232,12 +232,13 @@ __global__ void __launch_bounds__(THREADS, 1) head_dgrad_tc_kernel(const __grid_
                     const float g = df[8 * j + e] * inv_T * gelu_grad_fast(y);
                     v[e] = live ? g : 0.f;
                 }
-                if (own && a.write_dy4) {
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) dy4[(size_t)(8 * j + e) * a.TS + t] = v[e];
-                }
                 uint4 o[NT];
                 split8<NT>(v, o);
+                if (own && a.write_dy4) {                           // operand image for the weight-gradient kernel (see below)
+#pragma unroll
+                    for (int tm = 0; tm < 2; ++tm)
+                        *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(dy4) + ((size_t)(tm * 4 + j) * a.T_out + t) * 16) = o[tm];
+                }
 #pragma unroll
                 for (int tm = 0; tm < NT; ++tm) *reinterpret_cast<uint4*>(yt + tm * (4 * RY * 16) + j * (RY * 16) + (m + 2) * 16) = o[tm];
             }
@@ -278,12 +279,15 @@ __global__ void __launch_bounds__(THREADS, 1) head_dgrad_tc_kernel(const __grid_
                     unpk(sum, v[i], v[i + 1]);
                 }
         };
-        auto save_rows = [&](const float (&v)[CW], int it, int stage) {
+        // dL/dy3 and dL/dy2 leave as split-bf16 OPERAND IMAGES -- [term 2][channel group 4][t < T_out][8 x bf16] inside the item's
+        // stage slot, exactly the B tile of head_wgrad_tc.cu -- not as fp32: the weight-gradient kernel then needs no conversion
+        // pass, its tiles are filled by bulk copies.  Each row is written by the stream that owns it.
+        auto save_image = [&](const uint4 (&o)[NT], int j, int it, int stage) {
             if (!own) return;
             const size_t item = (size_t)(rank + it * nz) * a.Z + z;
-            float* dst = a.dys + (item * 3 + stage) * item_sz + (size_t)(CW * h) * a.TS + t;
+            uint8_t* img = reinterpret_cast<uint8_t*>(a.dys + (item * 3 + stage) * item_sz);
 #pragma unroll
-            for (int i = 0; i < CW; ++i) dst[(size_t)i * a.TS] = v[i];
+            for (int tm = 0; tm < 2; ++tm) *reinterpret_cast<uint4*>(img + ((size_t)(tm * 4 + 2 * h + j) * a.T_out + t) * 16) = o[tm];
         };
 #pragma unroll 1
         for (int it = 0; it < n_it; ++it) {
@@ -303,19 +307,27 @@ __global__ void __launch_bounds__(THREADS, 1) head_dgrad_tc_kernel(const __grid_
                     split8<NT>(x8, o);
 #pragma unroll
                     for (int tm = 0; tm < NT; ++tm) *reinterpret_cast<uint4*>(yt + tm * (4 * RY * 16) + j * (RY * 16)) = o[tm];
+                    save_image(o, j, it, 1);
                 }
                 fence_proxy_async();
                 tc_fence_before();
                 mbar_arrive(&sm.yb_ready[s]);
             }
-            save_rows(v, it, 1);
             // ---- dL/dy2: drain -> global
             group_wait(&sm.dm_full[s], 1);
             tc_fence_after();
             drain(v);
             tc_fence_before();
             mbar_arrive(&sm.d_free[s]);
-            save_rows(v, it, 2);
+#pragma unroll
+            for (int j = 0; j < CW / 8; ++j) {
+                float x8[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) x8[e] = v[8 * j + e];
+                uint4 o[NT];
+                split8<NT>(x8, o);
+                save_image(o, j, it, 2);
+            }
         }
     }
     tc_fence_before();

@@ -118,7 +118,8 @@ struct FwdArgs {
     const uint8_t* packed;
     const float* x;
     float* feat;
-    float* saved;                              // SAVE builds (training forward): per item 3 x [F][TS] fp32 y2, y3, y4, as head_fwd writes them
+    float* saved;                              // SAVE builds (training forward): per item 3 slots of F * TS floats: y2, y3 as split-bf16
+                                               // operand images, y4 as fp32 [F][TS] (the input-gradient kernel needs gelu'(y4))
     int TS;
     long long* prof;                           // PROF builds only: per-CTA wait-cycle counters [grid][16]
     int dbg;                                   // PROF builds only: bit0 skip operand stores, bit1 skip GELU, bit2 skip electrode loads
@@ -448,8 +449,15 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
 #pragma unroll
             for (int i = 0; i < CW; ++i) dst[(size_t)i * a.TS] = add_bias ? v[i] + be[i] : v[i];
         };
-        auto to_operand = [&](float (&v)[CW], bool add_bias, int it, uint64_t* ready) {
+        // SAVE (training forward), stage 0 / 1 (y2 / y3): the first two bf16 terms just computed ARE the operand image the
+        // weight-gradient kernel needs (head_wgrad_tc.cu: A operand, plane = term * 4 + channel group, one 16-byte row per time
+        // sample), so they are stored as such -- [term 2][channel group 4][t < T_out][8 x bf16] inside the item's stage slot
+        // (128 T_out bytes of its 128 TS) -- instead of as fp32: same bytes, four 16-byte stores per thread instead of sixteen
+        // scalar ones, and no fp32 -> bf16 conversion pass in the backward.  Each row is written by the stream that owns it.
+        auto to_operand = [&](float (&v)[CW], bool add_bias, int it, uint64_t* ready, int stage) {
             uint8_t* yt = yt0 + (it & 1) * y_bytes(NT);
+            uint8_t* img = nullptr;
+            if (SAVE && own) img = reinterpret_cast<uint8_t*>(a.saved + (((size_t)(rank + it * nz) * a.Z + z) * 3 + stage) * (size_t)(F * a.TS));
             if (!(PROF && (a.dbg & 1)))
 #pragma unroll
             for (int j = 0; j < CW / 8; ++j) {
@@ -464,6 +472,11 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
                 split8<NT>(x8, o);
 #pragma unroll
                 for (int tm = 0; tm < NT; ++tm) *reinterpret_cast<uint4*>(yt + tm * (4 * RY * 16) + j * (RY * 16)) = o[tm];
+                if (SAVE && img != nullptr) {
+#pragma unroll
+                    for (int tm = 0; tm < 2; ++tm)
+                        *reinterpret_cast<uint4*>(img + ((size_t)(tm * 4 + 2 * h + j) * a.T_out + t) * 16) = o[tm];
+                }
             }
             fence_proxy_async();
             tc_fence_before();
@@ -477,8 +490,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
             tc_fence_after();
             float v[CW];
             drain(lane_addr + (2 + s) * DCOLS, v);
-            to_operand(v, true, it, &sm.ye_ready[s]);
-            if (SAVE) save_rows(v, true, it, 0);
+            to_operand(v, true, it, &sm.ye_ready[s], 0);
             if (PROF) ep[0] += clock64() - c0;
         };
         auto epi_cnn3 = [&](int it) {
@@ -489,8 +501,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_fwd_tc_kernel(const __grid_co
             tc_fence_after();
             float v[CW];
             drain(lane_addr + s * DCOLS, v);
-            to_operand(v, false, it, &sm.yc_ready[s]);
-            if (SAVE) save_rows(v, false, it, 1);
+            to_operand(v, false, it, &sm.yc_ready[s], 1);
             if (PROF) ep[1] += clock64() - c0;
         };
         auto epi_cnn4 = [&](int it) {

@@ -68,45 +68,70 @@ struct Args {
     uint8_t cta_zone[NUM_SMS], cta_layer[NUM_SMS], cta_rank[NUM_SMS], cta_n[NUM_SMS];
 };
 
-struct Smem {
-    uint64_t stg_full[2], stg_empty[2], tile_full[2], tile_empty[2], done;
+// =====================================================================================================================
+// Image-fed kernel (round 2, the shipped one).
+//
+// The forward (head_tc.cu, SAVE) and the input-gradient kernel (head_dgrad_tc.cu) now leave y2, y3 and dL/dy4, dL/dy3,
+// dL/dy2 in HBM as the split-bf16 OPERAND IMAGES this kernel multiplies -- [term 2][channel group 4][t < T_out][8 x bf16],
+// i.e. plane p = term * 4 + group of the tiles above, one 16-byte row per time sample -- so there is no fp32 staging ring
+// and no conversion pass here: a producer lane fills the tiles of item i + 1 with bulk async copies (one per plane) while
+// the MMA warp works on item i.  That also makes the second tap free: the A planes are copied twice, the second time one
+// row earlier and directly behind the first copy (A2[p][r] = A[p][r + 1]), so the planes 8-15 that the M = 128 descriptor
+// reads anyway hold the same operand at tap + 1 -- lanes 0-63 accumulate tap 2j, lanes 64-127 tap 2j + 1, three MMAs per
+// K16 step instead of five (48 instead of 80 per item and layer; FB_WG_ONE_TAP keeps the five).
+// Only the collapsed-embed layer still converts: its A operand is the zone's raw electrodes (fp32 trials), gathered and
+// split by the eight converter warps (one time sample per thread, next item's 16 loads in flight), which also form the
+// collapsed-bias gradient sum_t dL/dy2 from the landed B planes.
+namespace im {
+
+constexpr int R = 264;                          // tile rows: 2 zero rows + up to 256 time samples + 5 tap rows (+ spare)
+constexpr int PLANE_I = R * 16;
+constexpr int TILE_I = 8 * PLANE_I;
+#ifdef FB_WG_ONE_TAP
+constexpr bool TWO_TAP = false;
+#else
+constexpr bool TWO_TAP = true;
+#endif
+constexpr int NTILE = TWO_TAP ? 3 : 2;          // [A | (A one row earlier) | B]
+constexpr int BUF_I = NTILE * TILE_I;
+constexpr int NBUF = TWO_TAP ? 2 : 3;           // 202,752 bytes of tiles either way
+constexpr int NACC = TWO_TAP ? 3 : TAPS;        // accumulators: tap pairs (0,1) (2,3) (4,-), or the five taps
+constexpr int TMEM_COLS_I = TWO_TAP ? 256 : 512;
+constexpr int CONV_T = 256, THREADS_I = CONV_T + 64;      // warp 0 producer, warp 1 MMA issuer, warps 2-9 converters / drain
+constexpr uint32_t DESC_HI_I = (uint32_t)(PLANE_I >> 4) | (1u << 14);
+
+struct SmemI {
+    uint64_t full[NBUF], empty[NBUF], bfull[NBUF], done;
     uint32_t tmem_base;
-    float bsum[F];                             // layer 2: sum_t dL/dy2 over the CTA's items (gradient of the collapsed bias)
+    float bsum[F];
 };
 
-__global__ void __launch_bounds__(THREADS, 1) head_wgrad_tc_kernel(const __grid_constant__ Args a) {
+__global__ void __launch_bounds__(THREADS_I, 1) head_wgrad_img_kernel(const __grid_constant__ Args a) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
-    uint8_t* tiles = smem_raw + HDR;                                // [buf][A | B]
-    uint8_t* stg = tiles + 4 * TILE;                                // [2 slots][F][TS] fp32
+    SmemI& sm = *reinterpret_cast<SmemI*>(smem_raw);
+    uint8_t* tiles = smem_raw + HDR;                                // [buf][A | A2 | B]
     const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
-    // layer 0: cnn3 (A = y2, B = dy3); 1: cnn4 (A = y3, B = dy4); 2: collapsed cnn1 o cnn2 (A = the zone's electrodes, B = dy2)
     const int z = a.cta_zone[blockIdx.x], layer = a.cta_layer[blockIdx.x];
     const bool emb = layer == 2;
     const int Cz = a.cz[z];
-    const int TSX = a.TS + 4;                                       // staging row stride of the electrode rows (W = T_out + 4 samples)
     const int rank = a.cta_rank[blockIdx.x], nc = a.cta_n[blockIdx.x];
     const int n_it = rank < a.BN ? (a.BN - rank + nc - 1) / nc : 0;
-    const uint32_t tensor_bytes = (uint32_t)(F * a.TS * 4);
-    const uint32_t slot_bytes = (uint32_t)(2 * 16 * (a.TS + 4) * 4);   // staging slot: one [F][TS] tensor, or two [16][TS + 4] electrode tiles
+    const size_t item_sz = (size_t)F * a.TS;                        // floats per stage slot
+    const uint32_t plane_bytes = (uint32_t)a.T_out * 16u;           // one plane of an image
 
     if (tid == 0) {
-        for (int i = 0; i < 2; ++i) {
-            mbar_init(&sm.stg_full[i], 1);
-            mbar_init(&sm.stg_empty[i], CONV_WARPS * 32);
-            mbar_init(&sm.tile_full[i], 2 * CONV_WARPS * 32);
-            mbar_init(&sm.tile_empty[i], 1);
+        for (int i = 0; i < NBUF; ++i) {
+            mbar_init(&sm.full[i], emb ? CONV_T : 1);
+            mbar_init(&sm.empty[i], 1);
+            mbar_init(&sm.bfull[i], 1);
         }
         mbar_init(&sm.done, 1);
         fence_mbar_init();
     }
-    for (int i = tid; i < 4 * TILE / 16; i += THREADS) reinterpret_cast<uint4*>(tiles)[i] = make_uint4(0, 0, 0, 0);
-    if (emb) {                                                      // electrode rows >= Cz of staging slot 0 stay zero
-        for (int i = tid; i < 2 * 16 * TSX; i += THREADS) reinterpret_cast<float*>(stg)[i] = 0.f;
-        if (tid < F) sm.bsum[tid] = 0.f;
-    }
+    for (int i = tid; i < NBUF * BUF_I / 16; i += THREADS_I) reinterpret_cast<uint4*>(tiles)[i] = make_uint4(0, 0, 0, 0);
+    if (tid < F) sm.bsum[tid] = 0.f;
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)), "n"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)), "n"(TMEM_COLS_I) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     fence_proxy_async();
@@ -114,25 +139,30 @@ __global__ void __launch_bounds__(THREADS, 1) head_wgrad_tc_kernel(const __grid_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = __shfl_sync(0xffffffffu, sm.tmem_base, 0);
-    const size_t item_sz = (size_t)F * a.TS;
 
     if (n_it > 0) {
         if (warp == 0) {
-            // ---------------- producer: tensor loads A(0), B(0), A(1), B(1), ... into the 2-slot staging ring
-            // (embed layer: only B = dy2 -- the electrode rows are gathered by the converter warps themselves)
+            // ---------------- producer: images -> tiles, one bulk async copy per plane
             if (lane == 0) {
-                for (int L = emb ? 1 : 0; L < 2 * n_it; L += emb ? 2 : 1) {
-                    const int slot = L & 1, it = L >> 1;
-                    if (L >= 2) mbar_wait(&sm.stg_empty[slot], ((L >> 1) - 1) & 1);
+                for (int it = 0; it < n_it; ++it) {
+                    const int buf = it % NBUF, use = it / NBUF;
+                    if (use >= 1) mbar_wait(&sm.empty[buf], (use - 1) & 1);
                     const size_t item = (size_t)(rank + it * nc) * a.Z + z;
-                    const bool recompute = slot == 1 && layer == 1 && a.dy4_from_y4;
-                    const float* src = slot == 0 ? a.saved + item * 3 * item_sz + (size_t)layer * item_sz              // y2 / y3
-                                     : recompute ? a.saved + item * 3 * item_sz + 2 * item_sz                          // y4 (-> dy4 in the converter)
-                                                 : a.dys + item * 3 * item_sz + (size_t)(emb ? 2 : 1 - layer) * item_sz;   // dy3 / dy4 / dy2
-                    mbar_expect_tx(&sm.stg_full[slot], tensor_bytes + (recompute ? (uint32_t)(F * 4) : 0u));
-                    bulk_g2s(stg + (size_t)slot * slot_bytes, src, tensor_bytes, &sm.stg_full[slot]);
-                    // the item's dfeat row rides behind the tensor in the slot's spare bytes (slot_bytes - tensor_bytes = 512)
-                    if (recompute) bulk_g2s(stg + (size_t)slot * slot_bytes + tensor_bytes, a.dfeat + item * F, F * 4, &sm.stg_full[slot]);
+                    uint8_t* A1 = tiles + buf * BUF_I;
+                    uint8_t* Bt = A1 + (NTILE - 1) * TILE_I;
+                    const uint8_t* srcB = reinterpret_cast<const uint8_t*>(a.dys + item * 3 * item_sz + (size_t)(emb ? 2 : 1 - layer) * item_sz);
+                    if (emb) {
+                        mbar_expect_tx(&sm.bfull[buf], 8 * plane_bytes);
+                        for (int p = 0; p < 8; ++p) bulk_g2s(Bt + p * PLANE_I, srcB + (size_t)p * plane_bytes, plane_bytes, &sm.bfull[buf]);
+                    } else {
+                        const uint8_t* srcA = reinterpret_cast<const uint8_t*>(a.saved + item * 3 * item_sz + (size_t)layer * item_sz);
+                        mbar_expect_tx(&sm.full[buf], (TWO_TAP ? 24u : 16u) * plane_bytes);
+                        for (int p = 0; p < 8; ++p) {
+                            bulk_g2s(A1 + p * PLANE_I + 2 * 16, srcA + (size_t)p * plane_bytes, plane_bytes, &sm.full[buf]);        // ypad: 2 zero rows in front
+                            if (TWO_TAP) bulk_g2s(A1 + TILE_I + p * PLANE_I + 1 * 16, srcA + (size_t)p * plane_bytes, plane_bytes, &sm.full[buf]);
+                            bulk_g2s(Bt + p * PLANE_I, srcB + (size_t)p * plane_bytes, plane_bytes, &sm.full[buf]);
+                        }
+                    }
                 }
             }
             __syncwarp();
@@ -140,148 +170,115 @@ __global__ void __launch_bounds__(THREADS, 1) head_wgrad_tc_kernel(const __grid_
             // ---------------- MMA issuer (converged warp, one elected lane inside umma_mn)
 #pragma unroll 1
             for (int it = 0; it < n_it; ++it) {
-                const int buf = it & 1;
-                mbar_wait(&sm.tile_full[buf], (it >> 1) & 1);
+                const int buf = it % NBUF, use = it / NBUF;
+                mbar_wait(&sm.full[buf], use & 1);
+                if (emb) mbar_wait(&sm.bfull[buf], use & 1);
                 tc_fence_after();
-                const uint32_t ad = (((smem_u32(tiles) + buf * 2 * TILE) & 0x3FFFFu) >> 4) | (a.lbo16 << 16);
-                const uint32_t bd = (((smem_u32(tiles) + buf * 2 * TILE + TILE) & 0x3FFFFu) >> 4) | (a.lbo16 << 16);
+                const uint32_t ad = (((smem_u32(tiles) + buf * BUF_I) & 0x3FFFFu) >> 4) | ((128u >> 4) << 16);
+                const uint32_t bd = (((smem_u32(tiles) + buf * BUF_I + (NTILE - 1) * TILE_I) & 0x3FFFFu) >> 4) | ((128u >> 4) << 16);
 #pragma unroll 1
                 for (int j = 0; j < a.ksteps; ++j) {
                     const uint32_t acc = (it > 0 || j > 0) ? 1u : 0u;
 #pragma unroll
-                    for (int k = 0; k < TAPS; ++k) umma_mn(tmem + k * NCOL, ad + 16 * j + k, bd + 16 * j, acc, a.desc_hi);
+                    for (int k = 0; k < NACC; ++k) umma_mn(tmem + k * NCOL, ad + 16 * j + (TWO_TAP ? 2 : 1) * k, bd + 16 * j, acc, DESC_HI_I);
                 }
-                umma_commit(&sm.tile_empty[buf]);
+                umma_commit(&sm.empty[buf]);
             }
             umma_commit(&sm.done);
         } else {
-            // ---------------- converters: staged fp32 [c][t] -> split-bf16 tile [term][c/8][row][8]
             const int ct = tid - 64;                                 // 0 .. 255
-            float bs[4][8];
-#pragma unroll
-            for (int p = 0; p < 4; ++p)
-#pragma unroll
-                for (int e = 0; e < 8; ++e) bs[p][e] = 0.f;
-#pragma unroll 1
-            // embed layer: fused unfold + zone gather of item `it` into electrode tile it & 1 of staging slot 0, by 4-byte
-            // cp.async (trial rows are only 4-byte aligned) spread over the 256 converter threads, one item ahead
-            auto gather = [&](int it) {
-                const int bn = rank + it * nc;
-                const int b = bn / a.n_win, n = bn - b * a.n_win;
-                const float* xb = a.x + (size_t)b * a.C * a.T + (size_t)n * a.step;
+            if (emb) {
+                // ---------------- embed layer: electrodes (fp32) -> split-bf16 A tile(s); collapsed-bias gradient from the B planes
                 const int* chan = a.chan + a.zoff[z];
-                const uint32_t dst0 = smem_u32(stg) + (uint32_t)(it & 1) * 16u * TSX * 4u;
-                for (int i = ct; i < Cz * a.W; i += CONV_WARPS * 32) {
-                    const int c = i / a.W, t = i - c * a.W;
-                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst0 + 4u * (c * TSX + t)), "l"(xb + (size_t)chan[c] * a.T + t) : "memory");
-                }
-                asm volatile("cp.async.commit_group;" ::: "memory");
-            };
-            if (emb) gather(0);
+                float bs[F];
+#pragma unroll
+                for (int c = 0; c < F; ++c) bs[c] = 0.f;
+                float cur[16], nxt[16];
+                auto load = [&](int it, float (&v)[16]) {            // unfold + zone gather: sample ct of the window, every electrode of the zone
+                    const int bn = rank + it * nc;
+                    const int b = bn / a.n_win, n = bn - b * a.n_win;
+                    const float* xb = a.x + (size_t)b * a.C * a.T + (size_t)n * a.step + ct;
+#pragma unroll
+                    for (int c = 0; c < 16; ++c) v[c] = (c < Cz && ct < a.W) ? __ldg(xb + (size_t)chan[c < Cz ? c : 0] * a.T) : 0.f;
+                };
+                load(0, cur);
 #pragma unroll 1
-            for (int it = 0; it < n_it; ++it) {
-                const int buf = it & 1;
-                if (emb) {
-                    asm volatile("cp.async.wait_group 0;" ::: "memory");                      // this thread's part of gather(it) landed
-                    asm volatile("bar.sync 1, %0;" ::"n"(CONV_WARPS * 32) : "memory");        // ... and everybody's; all are done with item it - 1
-                    if (it + 1 < n_it) gather(it + 1);                                        // tile (it + 1) & 1 was last read for item it - 1
-                }
-                // one polling warp (warp 2), the other seven converter warps park in named barrier 2: eight warps spinning on
-                // an mbarrier take the issue slots and shared-memory cycles the converting warps need (see head_tc.cu)
-#ifndef FB_NO_GROUP_WAIT_WG
-                if (it >= 2) {
-                    if (warp == 2) mbar_wait(&sm.tile_empty[buf], ((it >> 1) - 1) & 1);
-                    asm volatile("bar.sync 2, %0;" ::"n"(CONV_WARPS * 32) : "memory");
-                }
-#else
-                if (it >= 2) mbar_wait(&sm.tile_empty[buf], ((it >> 1) - 1) & 1);
-#endif
-#pragma unroll 1
-                for (int half = 0; half < 2; ++half) {
-                    const int L = 2 * it + half, slot = L & 1;
-#ifndef FB_NO_GROUP_WAIT_WG
-                    if (!(emb && half == 0)) {
-                        if (warp == 2) mbar_wait(&sm.stg_full[slot], (L >> 1) & 1);
-                        asm volatile("bar.sync 2, %0;" ::"n"(CONV_WARPS * 32) : "memory");
+                for (int it = 0; it < n_it; ++it) {
+                    const int buf = it % NBUF, use = it / NBUF;
+                    if (it + 1 < n_it) load(it + 1, nxt);            // in flight while this item is converted
+                    if (use >= 1) {
+                        if (warp == 2) mbar_wait(&sm.empty[buf], (use - 1) & 1);
+                        asm volatile("bar.sync 2, %0;" ::"n"(CONV_T) : "memory");
                     }
-#else
-                    if (!(emb && half == 0)) mbar_wait(&sm.stg_full[slot], (L >> 1) & 1);
-#endif
-                    const float* sg = (emb && half == 0) ? reinterpret_cast<const float*>(stg) + (it & 1) * 16 * TSX
-                                                         : reinterpret_cast<const float*>(stg + (size_t)slot * slot_bytes);
-                    if (emb && half == 0) {
-                        // electrodes: 16 channels (2 planes per term: a0 -> M rows 0-15, a1 -> 16-31), rows = samples 0 .. W-1
-                        uint8_t* tile = tiles + buf * 2 * TILE;
-                        for (int t = ct; t < a.W; t += CONV_WARPS * 32) {
+                    uint8_t* A1 = tiles + buf * BUF_I;
+                    if (ct < a.W) {
 #pragma unroll
-                            for (int p = 0; p < 2; ++p) {
-                                float v[8];
+                        for (int p = 0; p < 2; ++p) {                // 16 channels: planes 0, 1 hold term 0, planes 2, 3 term 1
+                            float v[8];
 #pragma unroll
-                                for (int e = 0; e < 8; ++e) v[e] = sg[(8 * p + e) * TSX + t];
-                                uint4 o[2];
-                                split8<2>(v, o);
-                                *reinterpret_cast<uint4*>(tile + p * PLANE + t * 16) = o[0];
-                                *reinterpret_cast<uint4*>(tile + (2 + p) * PLANE + t * 16) = o[1];
+                            for (int e = 0; e < 8; ++e) v[e] = cur[8 * p + e];
+                            uint4 o[2];
+                            split8<2>(v, o);
+                            *reinterpret_cast<uint4*>(A1 + p * PLANE_I + ct * 16) = o[0];
+                            *reinterpret_cast<uint4*>(A1 + (2 + p) * PLANE_I + ct * 16) = o[1];
+                            if (TWO_TAP && ct > 0) {
+                                *reinterpret_cast<uint4*>(A1 + TILE_I + p * PLANE_I + (ct - 1) * 16) = o[0];
+                                *reinterpret_cast<uint4*>(A1 + TILE_I + (2 + p) * PLANE_I + (ct - 1) * 16) = o[1];
                             }
                         }
-                    } else {
-                        uint8_t* tile = tiles + buf * 2 * TILE + half * TILE + (half == 0 ? 2 * 16 : 0);     // A rows are shifted by the 2 pad rows
-                        const bool recompute = half == 1 && layer == 1 && a.dy4_from_y4;
-                        const float* df = sg + F * a.TS;                                  // dfeat row behind the staged tensor
-                        const float inv_T = 1.0f / (float)a.T_out;
-                        for (int t = ct; t < a.T_out; t += CONV_WARPS * 32) {
+                    }
+                    // sum_t dL/dy2: this thread's time sample of all 32 channels, both bf16 terms, from the landed B planes -- BEFORE the
+                    // arrival below, so that the MMA (and with it the producer's refill of this buffer) cannot overtake the reads
+                    if (warp == 2) mbar_wait(&sm.bfull[buf], use & 1);
+                    asm volatile("bar.sync 2, %0;" ::"n"(CONV_T) : "memory");
+                    if (ct < a.T_out) {
+                        const uint8_t* Bt = A1 + (NTILE - 1) * TILE_I + ct * 16;
 #pragma unroll
-                            for (int p = 0; p < 4; ++p) {
-                                float v[8];
+                        for (int p = 0; p < 8; ++p) {
+                            const uint4 w = *reinterpret_cast<const uint4*>(Bt + p * PLANE_I);
+                            const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
-                                for (int e = 0; e < 8; ++e) v[e] = sg[(8 * p + e) * a.TS + t];
-                                if (recompute) {                    // same expression as head_dgrad_tc's first stage: bit-identical dL/dy4
-#pragma unroll
-                                    for (int e = 0; e < 8; ++e) v[e] = df[8 * p + e] * inv_T * gelu_grad_fast(v[e]);
-                                }
-                                if (emb) {
-#pragma unroll
-                                    for (int e = 0; e < 8; ++e) bs[p][e] += v[e];
-                                }
-                                uint4 o[2];
-                                split8<2>(v, o);
-                                *reinterpret_cast<uint4*>(tile + p * PLANE + t * 16) = o[0];
-                                *reinterpret_cast<uint4*>(tile + (4 + p) * PLANE + t * 16) = o[1];
+                            for (int i = 0; i < 4; ++i) {
+                                bs[8 * (p & 3) + 2 * i] += __uint_as_float(ww[i] << 16);
+                                bs[8 * (p & 3) + 2 * i + 1] += __uint_as_float(ww[i] & 0xffff0000u);
                             }
                         }
                     }
                     fence_proxy_async();
-                    if (!(emb && half == 0)) mbar_arrive(&sm.stg_empty[slot]);
-                    mbar_arrive(&sm.tile_full[buf]);
-                }
-            }
-            if (emb) {
+                    mbar_arrive(&sm.full[buf]);
+                    if (it + 1 < n_it) {
 #pragma unroll
-                for (int p = 0; p < 4; ++p)
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) {
-                        const float r = warp_sum(bs[p][e]);
-                        if (lane == 0) atomicAdd(&sm.bsum[8 * p + e], r);
+                        for (int c = 0; c < 16; ++c) cur[c] = nxt[c];
                     }
-                asm volatile("bar.sync 1, %0;" ::"n"(CONV_WARPS * 32) : "memory");
+                }
+#pragma unroll
+                for (int c = 0; c < F; ++c) {
+                    const float r = warp_sum(bs[c]);
+                    if (lane == 0) atomicAdd(&sm.bsum[c], r);
+                }
+                asm volatile("bar.sync 1, %0;" ::"n"(CONV_T) : "memory");
                 if (ct < F) atomicAdd(a.gpacked + a.boff[z] + ct, sm.bsum[ct]);
             }
-        }
-        // ---------------- drain: lanes 0-31 hold the a0 rows, 32-63 the a1 rows; columns [b0 | b1] per tap
-        if (warp < 2) {
-            mbar_wait(&sm.done, 0);
-            tc_fence_after();
-            float* g = a.gpacked + a.goff[z][layer];
-            if (!emb || warp == 0) {
-                const int row = emb ? (lane & 15) : lane;           // embed: lanes 0-15 = a0 rows, 16-31 = a1 rows (channel = lane & 15)
-                const bool ok = !emb || row < Cz;
+            // ---------------- drain by warps 4-7 = TMEM lane quadrants 0-3 (a warp may only read lanes 32 (warp % 4) .. + 31):
+            // TWO_TAP: quadrant 0 / 1 = a0 / a1 rows of the even tap of a pair, 2 / 3 of the odd tap; else quadrants 0 / 1 only.
+            // Embed layer: lanes 0-15 a0 rows, 16-31 a1 rows of quadrant 0 (and 2).
+            if (warp >= 4 && warp < 8) {
+                const int q4 = warp & 3;
+                mbar_wait(&sm.done, 0);
+                tc_fence_after();
+                float* g = a.gpacked + a.goff[z][layer];
+                const int odd = q4 >> 1;
+                const bool use = TWO_TAP ? (emb ? (q4 == 0 || q4 == 2) : true) : (emb ? q4 == 0 : q4 < 2);
+                const int row = emb ? (lane & 15) : lane;
+                const bool ok = use && (!emb || row < Cz);
 #pragma unroll 1
-                for (int k = 0; k < TAPS; ++k) {
+                for (int kk = 0; kk < NACC; ++kk) {
+                    const int k = TWO_TAP ? 2 * kk + odd : kk;
                     float v0[32], v1[32];
-                    const uint32_t addr = tmem + ((uint32_t)(32 * warp) << 16) + k * NCOL;
+                    const uint32_t addr = tmem + ((uint32_t)(32 * q4) << 16) + kk * NCOL;
                     tmem_ld32(addr, v0);
                     tmem_ld32(addr + 32, v1);
-                    if (ok) {
+                    if (ok && k < TAPS) {
 #pragma unroll
                         for (int co = 0; co < 32; ++co) atomicAdd(g + (row * TAPS + k) * F + co, v0[co] + v1[co]);
                     }
@@ -291,8 +288,10 @@ __global__ void __launch_bounds__(THREADS, 1) head_wgrad_tc_kernel(const __grid_
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS) : "memory");
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS_I) : "memory");
 }
+
+}  // namespace im
 
 }  // namespace wg
 }  // namespace fb
@@ -301,10 +300,12 @@ using namespace fb;
 
 static int wgrad_tc_supported(const fastb200_model* m) {
     FB_REQUIRE(m != nullptr, "model descriptor is NULL");
-    FB_REQUIRE(m->dim_cnn == wg::F, "tensor-core weight gradient needs dim_cnn == 32 (got %d)", m->dim_cnn);
+    FB_REQUIRE(m->dim_cnn == wg::F, "tensor-core backward needs dim_cnn == 32 (got %d)", m->dim_cnn);
     FB_REQUIRE(m->n_zones >= 1 && m->n_zones <= FASTB200_MAX_ZONES, "n_zones=%d out of range", m->n_zones);
-    const int T_out = m->window_len - 4;
-    FB_REQUIRE(T_out >= 16 && T_out <= 256, "tensor-core weight gradient needs 20 <= window_len <= 260 (got %d)", m->window_len);
+    // the backward consumes the operand images the tensor-core training forward writes: same shape envelope as that kernel
+    FB_REQUIRE(head_dgrad_tc_supported(m), "tensor-core backward needs 132 <= window_len <= 252 (got %d)", m->window_len);
+    for (int z = 0; z < m->n_zones; ++z)
+        FB_REQUIRE(m->zone_size[z] >= 1 && m->zone_size[z] <= 16, "zone %d has %d electrodes (tensor-core backward: 1..16)", z, m->zone_size[z]);
     return 0;
 }
 
@@ -312,7 +313,7 @@ extern "C" int fastb200_head_bwd_tc_supported(const fastb200_model* m) { return 
 
 extern "C" int64_t fastb200_head_bwd_tc_work_floats(const fastb200_model* m, int B, int n_win) {
     if (wgrad_tc_supported(m)) return -1;
-    // dL/dy4, dL/dy3, dL/dy2 per item + the split-bf16 transposed cnn3 / cnn4 weights of the tensor-core input-gradient kernel
+    // operand images of dL/dy4, dL/dy3, dL/dy2 per item + the split-bf16 transposed cnn3 / cnn4 weights of the input-gradient kernel
     return (int64_t)B * n_win * m->n_zones * 3 * m->dim_cnn * head_saved_stride(m->window_len) + head_dgrad_tc_packed_bytes(m, 3) / 4;
 }
 
@@ -323,34 +324,22 @@ extern "C" int fastb200_head_bwd_tc(const fastb200_model* m, const float* packed
     FB_REQUIRE(B >= 0 && n_win >= 1 && step >= 1, "bad B/n_win/step");
     FB_REQUIRE((n_win - 1) * (int64_t)step + m->window_len <= T, "windows run past the trial: n_win=%d step=%d W=%d T=%d", n_win, step, m->window_len, T);
     FB_REQUIRE((int64_t)B * n_win < (1ll << 31) / FASTB200_MAX_ZONES, "too many items for one launch");
+    FB_REQUIRE(dx == nullptr, "head_bwd_tc computes no input gradient: run fastb200_head_fwd + fastb200_head_bwd (CUDA cores) when dx is wanted");
     if (B == 0) return 0;
     FB_REQUIRE(packed && x && saved && dfeat && gpacked, "head_bwd_tc: NULL buffer");
     FB_REQUIRE(work != nullptr, "head_bwd_tc needs its workspace (fastb200_head_bwd_tc_work_floats)");
-    // the collapsed-embed weight / bias gradients join the tensor-core kernel when no input gradient is wanted (training) and
-    // every zone fits the 16-channel electrode tile; otherwise the CUDA-core kernel keeps them (and dx)
-    bool embed_tc = dx == nullptr;
-    for (int z = 0; z < m->n_zones; ++z) embed_tc = embed_tc && m->zone_size[z] <= 16;
-    int dg_terms = 2, dy4_from_y4 = 0;
-    bool dg_ffma = false;
+    int dg_terms = 2;
 #ifdef FASTB200_DEBUG
-    if (const char* dg_env = getenv("FASTB200_DGRAD")) {                              // developer builds: "ffma" forces the CUDA-core chain, "3" = 3 terms
-        dg_ffma = dg_env[0] == 'f';
-        if (atoi(dg_env) == 3) dg_terms = 3;
-    }
+    if (const char* dg_env = getenv("FASTB200_DGRAD")) if (atoi(dg_env) == 3) dg_terms = 3;        // developer builds: 3-term input-gradient chain
 #endif
-    if (embed_tc && head_dgrad_tc_supported(m) && !dg_ffma) {
-        float* pk = work + (int64_t)B * n_win * m->n_zones * 3 * m->dim_cnn * head_saved_stride(m->window_len);
-#ifndef FB_WRITE_DY4
-        dy4_from_y4 = 1;        // dL/dy4 is element-wise in y4: the weight-gradient kernel re-forms it, the 1.3 GB per 1024 trials stay off HBM
-#endif
-        if (int r = head_dgrad_tc_launch(m, packed, saved, dfeat, B, n_win, work, pk, dg_terms, /*write_dy4=*/!dy4_from_y4, stream)) return r;
-    } else if (int r = head_dgrad_launch(m, packed, x, saved, dfeat, B, T, n_win, step, gpacked, dx, work, embed_tc ? 1 : 0, stream)) return r;
+    float* pk = work + (int64_t)B * n_win * m->n_zones * 3 * m->dim_cnn * head_saved_stride(m->window_len);
+    if (int r = head_dgrad_tc_launch(m, packed, saved, dfeat, B, n_win, work, pk, dg_terms, /*write_dy4=*/1, stream)) return r;
     wg::Args a;
-    a.saved = saved; a.dys = work; a.gpacked = gpacked; a.x = x; a.dfeat = dfeat; a.dy4_from_y4 = dy4_from_y4;
+    a.saved = saved; a.dys = work; a.gpacked = gpacked; a.x = x; a.dfeat = dfeat; a.dy4_from_y4 = 0;
     a.BN = B * n_win; a.Z = m->n_zones; a.TS = head_saved_stride(m->window_len); a.T_out = m->window_len - 4;
     a.ksteps = ceil_div(a.T_out, 16);
     a.n_win = n_win; a.step = step; a.C = m->n_chan; a.T = T; a.W = m->window_len;
-    a.desc_hi = wg::DESC_HI_MN; a.lbo16 = 128u >> 4;
+    a.desc_hi = wg::im::DESC_HI_I; a.lbo16 = 128u >> 4;
     int n_sel = 0;
     for (int z = 0; z < m->n_zones; ++z) {
         const PackedZone p = packed_zone(*m, z);
@@ -358,7 +347,7 @@ extern "C" int fastb200_head_bwd_tc(const fastb200_model* m, const float* packed
         a.cz[z] = m->zone_size[z]; a.zoff[z] = m->zone_off[z]; n_sel += m->zone_size[z];
     }
     for (int i = 0; i < n_sel; ++i) a.chan[i] = m->zone_chan[i];
-    const int layers = embed_tc ? 3 : 2;
+    const int layers = 3;
     const int groups = layers * m->n_zones;                  // one (zone, layer) group per CTA; equal cost per item
     const int grid = NUM_SMS >= groups ? NUM_SMS : groups;
     int c = 0;
@@ -368,9 +357,9 @@ extern "C" int fastb200_head_bwd_tc(const fastb200_model* m, const float* packed
             a.cta_zone[c] = (uint8_t)(p / layers); a.cta_layer[c] = (uint8_t)(p % layers); a.cta_rank[c] = (uint8_t)r; a.cta_n[c] = (uint8_t)n;
         }
     }
-    const size_t smem = wg::HDR + 4 * wg::TILE + 2 * (size_t)(2 * 16 * (a.TS + 4) * 4);
-    cudaError_t e = cudaFuncSetAttribute(wg::head_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const size_t smem = wg::HDR + (size_t)wg::im::NBUF * wg::im::BUF_I;
+    cudaError_t e = cudaFuncSetAttribute(wg::im::head_wgrad_img_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return fail((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-    wg::head_wgrad_tc_kernel<<<grid, wg::THREADS, smem, as_stream(stream)>>>(a);
-    return check_launch("head_wgrad_tc");
+    wg::im::head_wgrad_img_kernel<<<grid, wg::im::THREADS_I, smem, as_stream(stream)>>>(a);
+    return check_launch("head_wgrad_img");
 }

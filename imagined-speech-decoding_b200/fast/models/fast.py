@@ -238,8 +238,14 @@ class _HeadFn(torch.autograd.Function):
             saved = None
             if need_grad:
                 saved = torch.empty(lib.fastb200_head_saved_floats(desc, B, n_win), device=xin.device, dtype=torch.float32)
-            if need_grad and n_terms and lib.fastb200_head_tc_supported(desc):
-                # training: tensor-core forward that also writes y2 / y3 / y4 for the backward kernels
+            # The saved activations come in two formats and the backward must match: the tensor-core training forward leaves
+            # split-bf16 operand images for the tensor-core backward (no input gradient); the CUDA-core forward leaves fp32
+            # tensors for the CUDA-core backward, which also forms dx (SHAP / input-gradient callers).
+            tc_train = (need_grad and n_terms and not ctx.needs_input_grad[0] and lib.fastb200_head_tc_supported(desc)
+                        and head_bwd_uses_tc(desc))
+            ctx.tc_train = bool(tc_train)
+            if tc_train:
+                # training: tensor-core forward that also writes y2 / y3 (operand images) and y4 for the backward kernels
                 packed_tc = torch.empty(lib.fastb200_head_packed_tc_bytes(desc, n_terms), device=xin.device, dtype=torch.uint8)
                 N.check(lib.fastb200_head_pack_tc(desc, N.ptr(flat), N.ptr(packed_tc), n_terms, st), "head_pack_tc")
                 N.check(lib.fastb200_head_fwd_tc_train(desc, N.ptr(packed_tc), N.ptr(xin), B, T, n_win, step, N.ptr(feat),
@@ -264,10 +270,10 @@ class _HeadFn(torch.autograd.Function):
             st = N.stream_ptr(xin.device)
             gpacked = torch.zeros_like(ctx.packed)
             dx = torch.zeros_like(xin) if need_dx else None
-            if head_bwd_uses_tc(desc):
+            if ctx.tc_train:
                 work = torch.empty(lib.fastb200_head_bwd_tc_work_floats(desc, B, ctx.n_win), device=xin.device, dtype=torch.float32)
                 N.check(lib.fastb200_head_bwd_tc(desc, N.ptr(ctx.packed), N.ptr(xin), N.ptr(ctx.saved), N.ptr(dfeat), B, T,
-                                                 ctx.n_win, ctx.step, N.ptr(gpacked), N.ptr(dx), N.ptr(work), st), "head_bwd_tc")
+                                                 ctx.n_win, ctx.step, N.ptr(gpacked), None, N.ptr(work), st), "head_bwd_tc")
             else:
                 N.check(lib.fastb200_head_bwd(desc, N.ptr(ctx.packed), N.ptr(xin), N.ptr(ctx.saved), N.ptr(dfeat), B, T,
                                               ctx.n_win, ctx.step, N.ptr(gpacked), N.ptr(dx), st), "head_bwd")

@@ -121,7 +121,7 @@ class FusedTrainer:
         d, dev, lib = self.desc, self.device, self.lib
         n_win = (T - d.window_len) // d.slide_step + 1
         n_terms = FM._TERMS[FM.get_head_precision()]
-        ws = dict(B=B, T=T, n_win=n_win, graph=None, p_drop=p_drop, grad_scale=float(self.grad_scale), fwd_terms=n_terms if (n_terms and lib.fastb200_head_tc_supported(d)) else 0,
+        ws = dict(B=B, T=T, n_win=n_win, graph=None, p_drop=p_drop, grad_scale=float(self.grad_scale), fwd_terms=0,
                   x=torch.empty(B, d.n_chan, T, device=dev),
                   y=torch.empty(B, device=dev, dtype=label_dtype),
                   feat=torch.empty(B, n_win, d.n_zones, d.dim_cnn, device=dev),
@@ -132,10 +132,17 @@ class FusedTrainer:
             ws["tr_saved"] = torch.empty(max(1, lib.fastb200_transformer_saved_floats(d, B, n_win)), device=dev)
             ws["dlogits"] = torch.empty(B, d.n_classes, device=dev)
             ws["dfeat"] = torch.empty_like(ws["feat"])
-            from ..models import fast as FM
             ws["bwd_work"] = None
-            if FM.head_bwd_uses_tc(d):
+        # The training forward and the backward are a pair: tensor-core forward (operand images saved) + tensor-core backward,
+        # or CUDA-core forward (fp32 saved) + CUDA-core backward.  With the head frozen nothing is saved and the
+        # tensor-core inference forward serves.
+        tc_fwd = bool(n_terms and lib.fastb200_head_tc_supported(d))
+        if train and not self.freeze_head:
+            if tc_fwd and FM.head_bwd_uses_tc(d):
+                ws["fwd_terms"] = n_terms
                 ws["bwd_work"] = torch.empty(lib.fastb200_head_bwd_tc_work_floats(d, B, n_win), device=dev)
+        elif tc_fwd:
+            ws["fwd_terms"] = n_terms
         self._ws[key] = ws
         return ws
 

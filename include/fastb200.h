@@ -145,23 +145,28 @@ int fastb200_head_fwd_tc(const fastb200_model* m, const void* packed, const floa
                          int step, float* feat, int n_terms, void* stream);
 
 /*
- * Training form of fastb200_head_fwd_tc: additionally writes the activations the backward needs (y2, y3, y4 per item, fp32,
- * the layout and size of fastb200_head_fwd's `saved`: fastb200_head_saved_floats) straight from the TMEM epilogues.
- * Only samples t < window_len - 4 of each [F][roundup4(W-4)] row are written; the backward kernels read nothing else.
+ * Training form of fastb200_head_fwd_tc: additionally writes, straight from the TMEM epilogues, what the tensor-core backward
+ * needs, into `saved` (fastb200_head_saved_floats: per item three slots of F * roundup4(W-4) floats):
+ *   slot 0 / 1: y2 / y3 as split-bf16 OPERAND IMAGES [term 2][channel group 4][t < W-4][8 x bf16] (128 (W-4) bytes of the slot) --
+ *               the A tiles of the weight-gradient MMAs, so the backward has no fp32 -> bf16 conversion pass;
+ *   slot 2:     y4 as fp32 [F][roundup4(W-4)] (the input-gradient chain starts with gelu'(y4)).
+ * This `saved` is for fastb200_head_bwd_tc ONLY; fastb200_head_bwd wants the all-fp32 `saved` of fastb200_head_fwd.
  */
 int fastb200_head_fwd_tc_train(const fastb200_model* m, const void* packed, const float* x, int B, int T, int n_win,
                                int step, float* feat, float* saved, int n_terms, void* stream);
 
 /* ---- zone embedding head backward with the cnn3 / cnn4 weight gradients on the tensor cores ------------------- */
 /*
- * Same function and arguments as fastb200_head_bwd (autograd of fast.py:111-119, 210, 247-251), split in two launches:
- * the CUDA-core kernel computes the input gradients of cnn4 / cnn3, the collapsed-embed weight / bias gradients and the
- * optional dx, and WRITES dL/dy4, dL/dy3 to `work`; a tcgen05 kernel then forms the cnn3 / cnn4 weight gradients
- * (per tap a (32 x T) x (T x 32) contraction over time, split-bf16 operands, fp32 accumulation in TMEM across all items).
- * Shapes supported: dim_cnn == 32, 20 <= window_len <= 260 (fastb200_head_bwd_tc_supported() returns 1).
- * When dx == NULL (training) and every zone has <= 16 electrodes the collapsed-embed weight / bias gradients are formed by
- * the tcgen05 kernel as well (A operand = the zone's electrodes, gathered from x by 4-byte cp.async).
- *   work: fastb200_head_bwd_tc_work_floats(m, B, n_win) floats (B*n_win*Z items x 3 x F x roundup4(W-4): dL/dy4, dL/dy3, dL/dy2).
+ * Autograd of Conv4Layers / Head / forward_head (fast.py:111-119, 210, 247-251) on the tensor cores, two launches:
+ *   1. head_dgrad_tc: dL/dy4 = dfeat / T * gelu'(y4), then the two transposed convolutions as implicit GEMMs; leaves dL/dy4,
+ *      dL/dy3, dL/dy2 in `work` as split-bf16 operand images (same format as slots 0 / 1 of `saved`);
+ *   2. head_wgrad_img: every weight gradient of the head -- per tap a (32 x T) x (T x 32) contraction over time, operands
+ *      bulk-copied from the images straight into the MMA tiles, two taps per MMA, fp32 accumulation in TMEM across all items;
+ *      the collapsed-embed layer gathers its A operand (the zone's electrodes) from x and also forms the bias gradient.
+ * `saved` must come from fastb200_head_fwd_tc_train.  dx must be NULL: an input gradient (SHAP) is computed by
+ * fastb200_head_fwd + fastb200_head_bwd.  Shapes: dim_cnn == 32, 132 <= window_len <= 252, zones of 1..16 electrodes
+ * (fastb200_head_bwd_tc_supported() returns 1).
+ *   work: fastb200_head_bwd_tc_work_floats(m, B, n_win) floats.
  */
 int     fastb200_head_bwd_tc_supported(const fastb200_model* m);
 int64_t fastb200_head_bwd_tc_work_floats(const fastb200_model* m, int B, int n_win);
