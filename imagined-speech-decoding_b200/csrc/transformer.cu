@@ -9,30 +9,13 @@
 // LayerNorm / softmax reductions are warp shuffles; dropout masks come from a counter-based generator so the
 // backward kernel regenerates them instead of storing them.
 #include "common.cuh"
+#include "transformer.cuh"
 #include <cstdlib>
 
 namespace fb {
 
 constexpr int TR_THREADS = 512;
 constexpr int TR_WARPS = TR_THREADS / 32;
-constexpr float LN_EPS = 1e-5f;
-
-enum { ACT_NONE = 0, ACT_GELU = 1 };
-enum { SITE_ATTN = 0, SITE_FFN_HID = 1, SITE_FFN_OUT = 2, SITE_FINAL = 3 };
-
-struct DropCtx {
-    float p, scale;          // p == 0 -> identity
-    uint64_t seed, offset;
-    const int32_t* step_dev; // optional device counter added to offset (lets a replayed CUDA graph draw fresh masks)
-    __device__ __forceinline__ void resolve() {
-        if (p > 0.f && step_dev != nullptr) offset += (uint64_t)(uint32_t)__ldg(step_dev);
-    }
-    __device__ __forceinline__ float mask(int layer, int site, int trial, int elem) const {
-        if (p <= 0.f) return 1.f;
-        const uint64_t idx = ((uint64_t)(layer * 4 + site) << 44) + ((uint64_t)trial << 20) + (uint64_t)elem;
-        return uniform01(seed, offset, idx) >= p ? scale : 0.f;
-    }
-};
 
 // ---- shared-memory resident building blocks (all threads of the CTA call these; R = live rows) --------------
 // Asynchronous (cp.async, 4 bytes: the padded pitch breaks 16-byte alignment): a load -> store loop through registers
@@ -325,18 +308,6 @@ __device__ __forceinline__ void block_fwd(const fastb200_model& m, const float* 
 // ---------------------------------------------------------------------------------------------------------
 // forward kernel
 // ---------------------------------------------------------------------------------------------------------
-struct TrArgs {
-    const float* params;
-    const float* feat;      // (B, n_win, ZF)
-    float* logits;          // (B, NC)
-    float* saved;           // (B, L+1, tok, D) or null
-    const float* dlogits;   // backward only
-    float* grads;           // backward only (flat, accumulated)
-    float* dfeat;           // backward only, may be null
-    int B, n_win, tok, G, mode;
-    DropCtx dc;
-    int ws_floats;          // weight staging area
-};
 
 __device__ __forceinline__ int tr_ws_floats(const fastb200_model& m) {
     const int D = m.dim_token, Hd = m.dim_hidden, ZF = m.n_zones * m.dim_cnn;
@@ -668,6 +639,14 @@ static int pick_group(const fastb200_model& m, int B, int tok, int n_win, SizeFn
     return G;
 }
 
+// production shape -> one warp per trial (transformer_warp.cu); anything else -> the CTA-per-group kernels of this file
+static bool use_warp_path(const fastb200_model& m, const float* params, const float* feat, int n_win, int mode) {
+#ifdef FASTB200_DEBUG
+    if (const char* e = getenv("FASTB200_TR_GENERIC")) if (atoi(e) > 0) return false;        // developer builds: A/B probe
+#endif
+    return (reinterpret_cast<uintptr_t>(feat) & 15) == 0 && tw_supported(m, params, n_win, mode) != 0;
+}
+
 }  // namespace fb
 
 using namespace fb;
@@ -686,6 +665,7 @@ extern "C" int fastb200_transformer_fwd(const fastb200_model* m, const float* pa
     a.params = params; a.feat = feat; a.logits = logits; a.saved = saved;
     a.B = B; a.n_win = n_win; a.tok = n_win + 1; a.mode = mode;
     a.dc.p = dropout_p; a.dc.scale = dropout_p > 0.f ? 1.0f / (1.0f - dropout_p) : 1.f; a.dc.seed = seed; a.dc.offset = offset; a.dc.step_dev = dropout_step_dev;
+    if (use_warp_path(*m, params, feat, n_win, mode)) return tw_fwd_launch(*m, a, stream);
     a.ws_floats = host_ws_floats(*m);
     const size_t budget = 100 * 1024;
     FB_REQUIRE(fwd_smem_floats(*m, 1, a.tok, n_win) * sizeof(float) <= 227 * 1024, "sequence too long for the shared-memory resident transformer");

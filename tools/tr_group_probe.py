@@ -1,4 +1,5 @@
-"""Dev: token-path kernel time against the trials-per-CTA group G (debug build: FASTB200_TR_GROUP is read per call).
+"""Dev: token-path kernel time: warp-per-trial kernels (G = 0) against the CTA-per-group kernels with G trials per CTA
+(debug build: FASTB200_TR_GENERIC / FASTB200_TR_GROUP are read per call; GROUPS=0,1,4 selects).
 usage: FASTB200_LIB=tools/variants/dbg/libfastb200.so python tools/tr_group_probe.py"""
 import os, sys, types
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -19,8 +20,10 @@ def timed(fn, n=20):
     return e0.elapsed_time(e1) / n * 1e3
 for B in (64, 256, 1024, 8192):
     feat = torch.randn(B, 5, len(Zones), 32, device="cuda")
-    for G in (1, 2, 3, 4, 5, 6, 7, 8, 10, 12, 14, 16):
-        os.environ["FASTB200_TR_GROUP"] = str(G)
+    for G in (os.environ.get("GROUPS", "0").split(",")):
+        G = int(G)
+        if G > 0: os.environ["FASTB200_TR_GROUP"] = str(G)
+        os.environ["FASTB200_TR_GENERIC"] = "1" if G > 0 else "0"
         model.eval()
         with torch.no_grad():
             f = timed(lambda: model.forward_transformer(feat))
