@@ -363,3 +363,53 @@ extern "C" int fastb200_head_bwd_tc(const fastb200_model* m, const float* packed
     wg::im::head_wgrad_img_kernel<<<grid, wg::im::THREADS_I, smem, as_stream(stream)>>>(a);
     return check_launch("head_wgrad_img");
 }
+
+// ---- allocation-free form of fastb200_head_bwd_tc ------------------------------------------------------------------------
+// The workspace of the call above lives in a file-scope device array instead of a caller allocation, for callers that may not
+// allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  Every GPU that loads the library holds the
+// array until exit.  In host code `g_bwd_tc_static_work` is only a stand-in for the symbol: its device address is looked up once
+// per device with cudaGetSymbolAddress (with that device current) and that pointer is what the kernels receive.
+constexpr int64_t STATIC_WORK_FLOATS = (int64_t)FASTB200_HEAD_BWD_TC_STATIC_BYTES / 4;
+static __device__ __align__(256) float g_bwd_tc_static_work[STATIC_WORK_FLOATS];
+
+constexpr int STATIC_MAX_DEVICES = 64;
+static float* g_static_work_ptr[STATIC_MAX_DEVICES];                 // per device: address of the array on that device (0 = not looked up yet)
+
+static int static_work_address(float** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fb::fail((int)e, "cudaGetDevice: %s", cudaGetErrorString(e));
+    if (dev < 0 || dev >= STATIC_MAX_DEVICES) return fb::fail(-1, "device ordinal %d outside the static-workspace table (%d)", dev, STATIC_MAX_DEVICES);
+    float* p = __atomic_load_n(&g_static_work_ptr[dev], __ATOMIC_ACQUIRE);
+    if (p == nullptr) {
+        void* sym = nullptr;
+        e = cudaGetSymbolAddress(&sym, g_bwd_tc_static_work);        // the address on the CURRENT device
+        if (e != cudaSuccess) return fb::fail((int)e, "cudaGetSymbolAddress(static workspace): %s", cudaGetErrorString(e));
+        if (sym == nullptr) return fb::fail(-1, "cudaGetSymbolAddress returned a null address for the static workspace");
+        p = static_cast<float*>(sym);
+        __atomic_store_n(&g_static_work_ptr[dev], p, __ATOMIC_RELEASE);   // racing threads look up the same value
+    }
+    *out = p;
+    return 0;
+}
+
+extern "C" int64_t fastb200_head_bwd_tc_static_max_floats(void) { return STATIC_WORK_FLOATS; }
+
+extern "C" int fastb200_head_bwd_tc_static(const fastb200_model* m, const float* packed, const float* x, const float* saved,
+                                           const float* dfeat, int B, int T, int n_win, int step, float* gpacked, void* stream) {
+    using namespace fb;
+    FB_REQUIRE(m != nullptr, "model descriptor is NULL");
+    FB_REQUIRE(B >= 0 && n_win >= 1, "bad B/n_win");
+    const int64_t need = fastb200_head_bwd_tc_work_floats(m, B, n_win);
+    if (need < 0) return -1;                                          // unsupported shape: message already set
+    FB_REQUIRE(need <= STATIC_WORK_FLOATS,
+               "head_bwd_tc_static: B=%d x n_win=%d needs %lld workspace floats, the static workspace holds %lld (%d MiB): "
+               "use fastb200_head_bwd_tc with a caller workspace, or split the batch",
+               B, n_win, (long long)need, (long long)STATIC_WORK_FLOATS, (int)(FASTB200_HEAD_BWD_TC_STATIC_BYTES >> 20));
+    if (B == 0) return 0;
+    float* work = nullptr;
+    if (int r = static_work_address(&work)) return r;
+    // nothing in the workspace has to start at zero: the input-gradient kernel writes every image row the weight-gradient
+    // kernel reads and the transposed weights are re-packed per call, so the previous call's contents are simply overwritten
+    return fastb200_head_bwd_tc(m, packed, x, saved, dfeat, B, T, n_win, step, gpacked, /*dx=*/nullptr, work, stream);
+}

@@ -61,6 +61,8 @@ SIGNATURES = {
     "fastb200_head_bwd_tc_supported": (C.c_int, [_MP]),
     "fastb200_head_bwd_tc_work_floats": (C.c_int64, [_MP, C.c_int, C.c_int]),
     "fastb200_head_bwd_tc": (C.c_int, [_MP, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P]),
+    "fastb200_head_bwd_tc_static_max_floats": (C.c_int64, []),
+    "fastb200_head_bwd_tc_static": (C.c_int, [_MP, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
     "fastb200_head_tc_supported": (C.c_int, [_MP]),
     "fastb200_head_packed_tc_bytes": (C.c_int64, [_MP, C.c_int]),
     "fastb200_head_pack_tc": (C.c_int, [_MP, _P, _P, C.c_int, _P]),

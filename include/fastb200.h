@@ -173,6 +173,22 @@ int64_t fastb200_head_bwd_tc_work_floats(const fastb200_model* m, int B, int n_w
 int fastb200_head_bwd_tc(const fastb200_model* m, const float* packed, const float* x, const float* saved,
                          const float* dfeat, int B, int T, int n_win, int step, float* gpacked, float* dx,
                          float* work, void* stream);
+/*
+ * Allocation-free form of fastb200_head_bwd_tc.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  Same arguments and results as fastb200_head_bwd_tc with dx == NULL, but the workspace is a
+ * file-scope device array of FASTB200_HEAD_BWD_TC_STATIC_BYTES inside the library (every GPU that loads the library holds
+ * it until exit); the call performs no cudaMalloc / cudaFree and calls no allocating library routine.
+ *   limit: fastb200_head_bwd_tc_work_floats(m, B, n_win) <= fastb200_head_bwd_tc_static_max_floats()  (production shape:
+ *          B <= 8 trials of 5 windows x 8 zones); larger calls return -1 with a message naming both sizes.
+ *   The array is shared by every call on a device and keeps the previous call's contents; nothing in it has to start at
+ *   zero (each call overwrites what it reads).  Calls that overlap on the GPU (two streams, two threads) RACE on it:
+ *   serialise them, or use fastb200_head_bwd_tc with one workspace per stream.
+ */
+#define FASTB200_HEAD_BWD_TC_STATIC_BYTES (32ll << 20)
+int64_t fastb200_head_bwd_tc_static_max_floats(void);
+int fastb200_head_bwd_tc_static(const fastb200_model* m, const float* packed, const float* x, const float* saved,
+                                const float* dfeat, int B, int T, int n_win, int step, float* gpacked, void* stream);
 
 /* ---- transformer (input_layer, CLS, pos, L x AttentionBlock, last_layer) --------------------------------- */
 /* Floats saved per forward for the backward: B * (n_layers + 1) * n_tok * D  (block inputs + final tokens). */
