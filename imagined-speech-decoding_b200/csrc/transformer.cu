@@ -640,11 +640,11 @@ static int pick_group(const fastb200_model& m, int B, int tok, int n_win, SizeFn
 }
 
 // production shape -> one warp per trial (transformer_warp.cu); anything else -> the CTA-per-group kernels of this file
-static bool use_warp_path(const fastb200_model& m, const float* params, const float* feat, int n_win, int mode) {
+static bool use_warp_path(const fastb200_model& m, const float* params, const float* feat, int n_win, int mode, int backward = 0) {
 #ifdef FASTB200_DEBUG
     if (const char* e = getenv("FASTB200_TR_GENERIC")) if (atoi(e) > 0) return false;        // developer builds: A/B probe
 #endif
-    return (reinterpret_cast<uintptr_t>(feat) & 15) == 0 && tw_supported(m, params, n_win, mode) != 0;
+    return (reinterpret_cast<uintptr_t>(feat) & 15) == 0 && tw_supported(m, params, n_win, mode, backward) != 0;
 }
 
 }  // namespace fb
@@ -688,6 +688,9 @@ extern "C" int fastb200_transformer_bwd(const fastb200_model* m, const float* pa
     a.params = params; a.feat = feat; a.saved = const_cast<float*>(saved); a.dlogits = dlogits; a.grads = grads; a.dfeat = dfeat;
     a.B = B; a.n_win = n_win; a.tok = n_win + 1; a.mode = mode;
     a.dc.p = dropout_p; a.dc.scale = dropout_p > 0.f ? 1.0f / (1.0f - dropout_p) : 1.f; a.dc.seed = seed; a.dc.offset = offset; a.dc.step_dev = dropout_step_dev;
+    if (((reinterpret_cast<uintptr_t>(grads) | reinterpret_cast<uintptr_t>(dfeat) | reinterpret_cast<uintptr_t>(saved)) & 15) == 0 &&
+        use_warp_path(*m, params, feat, n_win, mode, 1))
+        return tw_bwd_launch(*m, a, stream);
     a.ws_floats = host_ws_floats(*m);
     const size_t budget = 160 * 1024;
     FB_REQUIRE(bwd_smem_floats(*m, 1, a.tok, n_win) * sizeof(float) <= 227 * 1024, "sequence too long for the shared-memory resident transformer backward");

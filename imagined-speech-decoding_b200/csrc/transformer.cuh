@@ -40,9 +40,9 @@ struct TrArgs {
 // ---- warp-per-trial kernels (transformer_warp.cu) -----------------------------------------------------------------------
 // 1 when the shape is covered: dim_token 32, 8 heads, hidden 64, n_win + 1 tokens in [2, 8], 16-byte aligned parameter blocks
 // and a shared-memory footprint that fits.
-int tw_supported(const fastb200_model& m, const float* params, int n_win, int mode);
+int tw_supported(const fastb200_model& m, const float* params, int n_win, int mode, int backward);
 int tw_fwd_launch(const fastb200_model& m, const TrArgs& a, void* stream);
-int64_t tw_bwd_work_floats(const fastb200_model& m, int B, int n_win);
-int tw_bwd_launch(const fastb200_model& m, const TrArgs& a, float* work, void* stream);
+// backward: mode 'default' only, 16-byte aligned grads / dfeat; gradients are ACCUMULATED into a.grads like transformer_bwd
+int tw_bwd_launch(const fastb200_model& m, const TrArgs& a, void* stream);
 
 }  // namespace fb

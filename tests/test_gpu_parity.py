@@ -495,6 +495,50 @@ def test_dropout_train_mode_is_consistent():
         assert torch.equal(m(x), m(x))
 
 
+@pytest.mark.parametrize("B", [1, 7, 64, 301, 700, 2500])
+def test_token_path_backward_vs_oracle_autograd_every_schedule(B):
+    """fastb200_transformer_fwd / _bwd through the C ABI against fp64 autograd of the oracle's forward_transformer: batch sizes
+    that run the 6-warps-per-trial schedule (one slot, two slots with an idle one, several rounds) and the warp-per-trial
+    schedule (partly filled CTAs, several rounds).  All gradients of the token path, dfeat, and accumulation into `grads`."""
+    from fast import _native as N
+    m = _prod_model(dropout=0.0).eval()
+    cfg = make_prod_cfg(dropout=0.0)
+    flat, desc = m._runtime()
+    lib = N.lib()
+    n_win = 5
+    gen = torch.Generator(device='cuda').manual_seed(100 + B)
+    feat = torch.randn(B, n_win, 8, 32, device='cuda', generator=gen)
+    w = torch.randn(B, 5, device='cuda', generator=gen) / B
+    logits = torch.empty(B, 5, device='cuda')
+    saved = torch.empty(lib.fastb200_transformer_saved_floats(desc, B, n_win), device='cuda')
+    N.check(lib.fastb200_transformer_fwd(desc, N.ptr(flat), N.ptr(feat), B, n_win, 0, 0.0, 0, 0, None, N.ptr(logits), N.ptr(saved),
+                                         N.stream_ptr()), "tfwd")
+    base = torch.randn(flat.numel(), device='cuda', generator=gen) * 1e-3            # the call ACCUMULATES into grads
+    grads = base.clone()
+    dfeat = torch.full_like(feat, float('nan'))
+    N.check(lib.fastb200_transformer_bwd(desc, N.ptr(flat), N.ptr(feat), N.ptr(saved), N.ptr(w), B, n_win, 0, 0.0, 0, 0, None,
+                                         N.ptr(grads), N.ptr(dfeat), N.stream_ptr()), "tbwd")
+    sd = {k: v.detach().double().clone().requires_grad_(not k.startswith("head.")) for k, v in m.state_dict().items()
+          if v.is_floating_point()}
+    f64 = feat.double().requires_grad_(True)
+    ref = O.forward_transformer(sd, cfg, f64)
+    assert rel_err(logits, ref.detach()) < TOL
+    (ref * w.double()).sum().backward()
+    assert rel_err(dfeat, f64.grad) < TOL
+    got = grads - base
+    for name, _, off, cnt in m._fp.items:
+        if name.startswith("head."):
+            assert torch.equal(got[off:off + cnt], torch.zeros_like(got[off:off + cnt])), name
+            continue
+        e = rel_err(got[off:off + cnt], sd[name].grad.reshape(-1))
+        assert e < TOL, (name, e)
+    # head frozen ('train_transformer'): no dfeat wanted
+    g2 = torch.zeros_like(flat)
+    N.check(lib.fastb200_transformer_bwd(desc, N.ptr(flat), N.ptr(feat), N.ptr(saved), N.ptr(w), B, n_win, 0, 0.0, 0, 0, None,
+                                         N.ptr(g2), None, N.stream_ptr()), "tbwd (no dfeat)")
+    assert rel_err(g2, got) < 1e-5
+
+
 # ---------------------------------------------------------------------------------------------- tensor-core head
 # fastb200_head_fwd_tc (split-bf16 tcgen05 MMAs) against the fp64 oracle.  Bounds: 3 terms = 24 mantissa bits (fp32
 # equivalent; the residual is the 1.5e-7 erfc approximation of the fused GELU), 2 terms = 16 bits.  Both far inside TOL.
