@@ -497,19 +497,28 @@ __host__ __device__ inline BLay make_blay(const fastb200_model& m, int n_win, in
 // dx[o][r] += sum_{j < DOUT} ys[r][j] * W[j][lane + 32 (o0 + o)]       (W: DOUT rows of `cols` floats, swizzled)
 template <int NR, int NO, int DOUT>
 __device__ __forceinline__ void dgrad_rows(const float* W, int cols, int o0, const float* ys, int ldy, float (&dx)[NO][NR], int lane) {
-#pragma unroll 2
-    for (int j4 = 0; j4 < DOUT / 4; ++j4) {
-        float4 y[NR];
+    static_assert(DOUT % 8 == 0, "rows are walked in groups of 8 (the period of the swizzle)");
+    int lo[8];                                           // column lane + 32 o of row j sits at 32 o + lo[j & 7]
 #pragma unroll
-        for (int r = 0; r < NR; ++r) y[r] = *reinterpret_cast<const float4*>(ys + r * ldy + 4 * j4);
+    for (int jj = 0; jj < 8; ++jj) lo[jj] = ((((lane >> 2) ^ jj) << 2) | (lane & 3)) + 32 * o0;
+#pragma unroll 1
+    for (int j8 = 0; j8 < DOUT / 8; ++j8) {
+        const float* Wj = W + 8 * j8 * cols;
+        float4 y[2][NR];
 #pragma unroll
-        for (int jj = 0; jj < 4; ++jj) {
+        for (int r = 0; r < NR; ++r) {
+            y[0][r] = *reinterpret_cast<const float4*>(ys + r * ldy + 8 * j8);
+            y[1][r] = *reinterpret_cast<const float4*>(ys + r * ldy + 8 * j8 + 4);
+        }
+#pragma unroll
+        for (int jj = 0; jj < 8; ++jj) {
             float wv[NO];
 #pragma unroll
-            for (int o = 0; o < NO; ++o) wv[o] = wcol(W, cols, 4 * j4 + jj, lane + 32 * (o0 + o));
+            for (int o = 0; o < NO; ++o) wv[o] = Wj[jj * cols + 32 * o + lo[jj]];
 #pragma unroll
             for (int r = 0; r < NR; ++r) {
-                const float yv = jj == 0 ? y[r].x : jj == 1 ? y[r].y : jj == 2 ? y[r].z : y[r].w;
+                const float4 yq = y[jj >> 2][r];
+                const float yv = (jj & 3) == 0 ? yq.x : (jj & 3) == 1 ? yq.y : (jj & 3) == 2 ? yq.z : yq.w;
 #pragma unroll
                 for (int o = 0; o < NO; ++o) dx[o][r] = fmaf(yv, wv[o], dx[o][r]);
             }
@@ -942,6 +951,7 @@ int tw_fwd_launch(const fastb200_model& m, const TrArgs& a, void* stream) {
 
 int tw_bwd_launch(const fastb200_model& m, const TrArgs& a, void* stream) {
     Plan p = make_plan(a.B, 12);
+    if (p.S == 1) p.slots = MAX_WARPS;                   // the CTA-wide weight-gradient pass has one tile per thread of 8 warps
     while (p.slots > 1 && (size_t)make_blay(m, a.n_win, p.S, p.slots).total * sizeof(float) > SMEM_MAX) --p.slots;
     const BLay ly = make_blay(m, a.n_win, p.S, p.slots);
     if (p.S == 1) return launch_tw(tw_bwd_kernel<6, 1>, p.grid, ly, m, a, stream, "transformer_bwd_warp");
