@@ -41,8 +41,27 @@ class ModelDesc(C.Structure):
     ]
 
 
+ALT_MAX_STAGES = 6
+
+
+class AltStage(C.Structure):
+    """Mirror of ``struct fastb200_alt_stage``."""
+    _fields_ = [("kind", _i32), ("out_ch", _i32), ("k", _i32), ("pad", _i32), ("act", _i32), ("pool_kind", _i32), ("pool", _i32),
+                ("w_off", _i32), ("scale_off", _i32), ("shift_off", _i32)]
+
+
+class AltHeadDesc(C.Structure):
+    """Mirror of ``struct fastb200_alt_head`` (eval-mode chain of the alternative zone heads)."""
+    _fields_ = [("window_len", _i32), ("n_zones", _i32), ("n_stages", _i32), ("final_kind", _i32),
+                ("lin_in", _i32), ("lin_out", _i32), ("lin_w_off", _i32), ("lin_b_off", _i32),
+                ("stage", AltStage * ALT_MAX_STAGES),
+                ("zone_size", _i32 * MAX_ZONES), ("zone_off", _i32 * MAX_ZONES), ("zone_chan", _i32 * MAX_CHANS),
+                ("zone_base", C.c_int64 * MAX_ZONES)]
+
+
 _P = C.c_void_p
 _MP = C.POINTER(ModelDesc)
+_AP = C.POINTER(AltHeadDesc)
 # name -> (restype, argtypes); every symbol include/fastb200.h declares
 SIGNATURES = {
     "fastb200_version": (C.c_int, []),
@@ -68,6 +87,8 @@ SIGNATURES = {
     "fastb200_head_pack_tc": (C.c_int, [_MP, _P, _P, C.c_int, _P]),
     "fastb200_head_fwd_tc": (C.c_int, [_MP, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, C.c_int, _P]),
     "fastb200_head_fwd_tc_train": (C.c_int, [_MP, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P, C.c_int, _P]),
+    "fastb200_sizeof_alt_head": (C.c_int, []),
+    "fastb200_alt_head_fwd": (C.c_int, [_AP, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
     "fastb200_transformer_saved_floats": (C.c_int64, [_MP, C.c_int, C.c_int]),
     "fastb200_transformer_fwd": (C.c_int, [_MP, _P, _P, C.c_int, C.c_int, C.c_int, C.c_float, C.c_uint64, C.c_uint64,
                                            _P, _P, _P, _P]),
@@ -108,6 +129,8 @@ def lib():
             fn.argtypes = args
         if handle.fastb200_sizeof_model() != C.sizeof(ModelDesc):
             raise RuntimeError("fastb200_model layout mismatch between include/fastb200.h and fast/_native.py")
+        if handle.fastb200_sizeof_alt_head() != C.sizeof(AltHeadDesc):
+            raise RuntimeError("fastb200_alt_head layout mismatch between include/fastb200.h and fast/_native.py")
         _lib = handle
     return _lib
 

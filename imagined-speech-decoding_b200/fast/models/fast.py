@@ -23,6 +23,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from .. import _native as N
+from . import alt_fused
 
 __all__ = ["FAST", "AttentionBlock", "CVBlock", "Conv4Layers", "EEGNet_Encoder", "HeadConv_Paper_Version", "Head",
            "set_head_precision", "get_head_precision", "set_head_backward", "get_head_backward"]
@@ -539,6 +540,7 @@ class Head(nn.Module):
         self._fused = Head_cls is Conv4Layers
         self._feature_dim = feature_dim
         self._fp = None
+        self._alt = None
 
     def _zone_index(self):
         return [self.index_dict[a].tolist() for a in self.encoders.keys()]
@@ -548,10 +550,23 @@ class Head(nn.Module):
         return self._fused and _fused_head_ok(window_len, [len(v) for v in self.index_dict.values()], self._feature_dim,
                                               need_backward)
 
+    def alt_fused_ok(self) -> bool:
+        """True when an alternative head runs as the fused eval-mode kernel (fastb200_alt_head_fwd): eval mode (BatchNorm on
+        running statistics, Dropout off), no autograd graph wanted; training / gradients use the stock torch modules."""
+        return (not self._fused) and (not self.training) and (not torch.is_grad_enabled()) and alt_fused.supported(self) and \
+            not any(m.training for m in self.modules())
+
+    def _alt_runner(self):
+        if self._alt is None:
+            self._alt = alt_fused.FusedAltHead(self)
+        return self._alt
+
     def forward(self, x):
         """x (R, C, T) -> (R, Z, F)."""
         if not self._fused:
             N.require_cuda(x, "input")
+            if self.alt_fused_ok():
+                return self._alt_runner().forward(x, x.shape[2], 1)[:, 0]
             return torch.stack([enc(x[:, self.index_dict[a].to(x.device)]) for a, enc in self.encoders.items()], dim=1)
         if not self.fused_ok(x.shape[2], torch.is_grad_enabled()):
             N.require_cuda(x, "input")
@@ -655,6 +670,8 @@ class FAST(nn.Module):
         step = self.config.slide_step if step_override is None else step_override
         if not self.head.fused_ok(self.config.window_len, torch.is_grad_enabled()):
             N.require_cuda(x, "input")
+            if self.head.alt_fused_ok():                 # alternative heads, eval mode: unfold + gather + all zones in one kernel
+                return self.head._alt_runner().forward(x, self.config.window_len, int(step))
             xw = x.unfold(-1, self.config.window_len, step)
             B, C, n, T = xw.shape
             feat = self.head(xw.permute(0, 2, 1, 3).reshape(B * n, C, T))

@@ -190,6 +190,47 @@ int64_t fastb200_head_bwd_tc_static_max_floats(void);
 int fastb200_head_bwd_tc_static(const fastb200_model* m, const float* packed, const float* x, const float* saved,
                                 const float* dfeat, int B, int T, int n_win, int step, float* gpacked, void* stream);
 
+/* ---- alternative zone heads, eval mode ---------------------------------------------------------------------- */
+/*
+ * Replaces Head.forward over CVBlock / EEGNet_Encoder / HeadConv_Paper_Version encoders (fast.py:32-100, 122-167, 170-196,
+ * 208-210) inside FAST.forward_head (fast.py:242-252) when the model is in eval mode: BatchNorm on its running statistics
+ * folds into a per-channel (scale, shift), Dropout is the identity, so each head is a chain of at most
+ * FASTB200_ALT_MAX_STAGES stages
+ *     out[o][t'] = pool( act( scale[o] * sum_{i,k} w[o][i][k] * in[i][t + k - pad] + shift[o] ) )
+ * (dense or depth-wise temporal conv, zero padded; pool stride = size in {1, 2, 4, 8}, floor) and a final temporal mean, mean + Linear or
+ * flatten + Linear.  All offsets are fp32 elements relative to zone_base[z] inside `packed`; stage 0 reads the zone's
+ * electrodes (in_ch = zone_size[z]), so its weights (out_ch, Cz, k) differ in size per zone.  Training mode (batch
+ * statistics, running-stat updates) is not covered: the Python modules run stock torch ops there.
+ */
+#define FASTB200_ALT_MAX_STAGES 6
+#define FASTB200_ALT_DENSE 0
+#define FASTB200_ALT_DEPTHWISE 1
+#define FASTB200_ALT_ACT_NONE 0
+#define FASTB200_ALT_ACT_ELU 1
+#define FASTB200_ALT_ACT_GELU 2
+#define FASTB200_ALT_POOL_NONE 0
+#define FASTB200_ALT_POOL_AVG 1
+#define FASTB200_ALT_POOL_MAX 2
+#define FASTB200_ALT_FINAL_MEAN 0
+#define FASTB200_ALT_FINAL_MEAN_LINEAR 1
+#define FASTB200_ALT_FINAL_FLATTEN_LINEAR 2
+typedef struct fastb200_alt_stage {
+    int32_t kind, out_ch, k, pad, act, pool_kind, pool;
+    int32_t w_off;                    /* output channel fastest -- dense: [in_ch][k][out_ch]; depth-wise: [k][out_ch], channel o reads input o / (out_ch / in_ch) */
+    int32_t scale_off, shift_off;     /* (out_ch) each; scale_off < 0: no affine */
+} fastb200_alt_stage;
+typedef struct fastb200_alt_head {
+    int32_t window_len, n_zones, n_stages, final_kind;
+    int32_t lin_in, lin_out, lin_w_off, lin_b_off;     /* Linear (lin_out, lin_in) + bias; FINAL_MEAN: lin_out = channels */
+    fastb200_alt_stage stage[FASTB200_ALT_MAX_STAGES];
+    int32_t zone_size[FASTB200_MAX_ZONES], zone_off[FASTB200_MAX_ZONES], zone_chan[FASTB200_MAX_CHANS];
+    int64_t zone_base[FASTB200_MAX_ZONES];
+} fastb200_alt_head;
+int fastb200_sizeof_alt_head(void);
+/*   x (B, C, T) -> feat (B, n_win, Z, lin_out); window n of trial b starts at sample n * step. */
+int fastb200_alt_head_fwd(const fastb200_alt_head* h, const float* packed, const float* x, int B, int C, int T, int n_win,
+                          int step, float* feat, void* stream);
+
 /* ---- transformer (input_layer, CLS, pos, L x AttentionBlock, last_layer) --------------------------------- */
 /* Floats saved per forward for the backward: B * (n_layers + 1) * n_tok * D  (block inputs + final tokens). */
 int64_t fastb200_transformer_saved_floats(const fastb200_model* m, int B, int n_win);

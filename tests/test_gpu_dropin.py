@@ -82,6 +82,58 @@ def test_alternative_heads_inside_fast_vs_reference(alt, head, no_tf32):
         assert rel_err(m.forward_head(x), alt[f"{head}/feat_eval"]) < TOL
 
 
+@pytest.mark.parametrize("head", ["CVBlock", "EEGNet_Encoder", "HeadConv_Paper_Version"])
+def test_alternative_heads_fused_eval_kernel_vs_stock_modules(head, no_tf32):
+    """fastb200_alt_head_fwd (eval mode: one launch for unfold + gather + every stage of every zone) against the stock torch
+    modules it replaces, production montage (8 zones of 4..15 electrodes), non-trivial BatchNorm statistics, a ragged batch,
+    the configured step and a step override; training mode and autograd keep the stock modules."""
+    from fast import _native as N
+    from fast.models import FAST
+    torch.manual_seed(3)
+    m = FAST(make_prod_cfg(head=head, dropout=0.0)).cuda()
+    g = torch.Generator().manual_seed(4)
+    for mod in m.modules():
+        if isinstance(mod, torch.nn.BatchNorm2d):
+            mod.running_mean.copy_(torch.randn(mod.num_features, generator=g) * 0.5)
+            mod.running_var.copy_(torch.rand(mod.num_features, generator=g) + 0.5)
+            mod.weight.data.copy_(torch.randn(mod.num_features, generator=g))
+            mod.bias.data.copy_(torch.randn(mod.num_features, generator=g) * 0.3)
+    m.eval()
+    x = (torch.randn(37, 64, 800, generator=g) * 3).cuda()
+    lib = N.lib()
+
+    def stock(step):
+        xw = x.unfold(-1, 250, step)
+        B, C, n, T = xw.shape
+        rows = xw.permute(0, 2, 1, 3).reshape(B * n, C, T)
+        f = torch.stack([enc(rows[:, m.head.index_dict[a].cuda()]) for a, enc in m.head.encoders.items()], dim=1)
+        return f.reshape(B, n, f.shape[1], f.shape[2])
+
+    with torch.no_grad():
+        for step in (125, 50):
+            n0 = lib.fastb200_launch_count()
+            got = m.forward_head(x, None if step == 125 else step)
+            assert lib.fastb200_launch_count() == n0 + 1              # the fused kernel ran, once
+            ref = stock(step)
+            assert got.shape == ref.shape
+            assert rel_err(got, ref) < TOL, (head, step, rel_err(got, ref))
+        rows = x[:, :, :250].contiguous()
+        assert rel_err(m.head(rows), stock(125)[:, 0]) < TOL          # Head.forward on (R, C, T) rows
+        # a parameter / buffer change invalidates the packed copy
+        first = next(iter(m.head.encoders.values()))
+        bn = next(mod for mod in first.modules() if isinstance(mod, torch.nn.BatchNorm2d))
+        bn.running_mean.add_(0.25)
+        assert rel_err(m.forward_head(x), stock(125)) < TOL
+        logits = m(x)
+        assert logits.shape == (37, 5) and bool(torch.isfinite(logits).all())
+    n0 = lib.fastb200_launch_count()
+    m.forward_head(x[:2])                                            # autograd wanted: stock modules
+    m.train()
+    with torch.no_grad():
+        m.forward_head(x[:2])                                        # training mode: batch statistics, stock modules
+    assert lib.fastb200_launch_count() == n0
+
+
 # ---------------------------------------------------------------------------------------------- trainer-facing module
 def _batches(n, b, seed):
     g = torch.Generator().manual_seed(seed)
