@@ -19,7 +19,7 @@ handle.fastb200_debug_set_tc_profile.argtypes = [ctypes.c_void_p]
 handle.fastb200_debug_set_tc_profile.restype = None
 names = ["mma total", "wait x_full", "wait d_free", "wait ye_ready", "wait yc_ready", "items", "epiA wait", "epiB wait",
          "epi embed (incl wait)", "epi cnn3 (incl wait)", "epi cnn4 after wait", "e4: drain+gelu+reduce", "e4: red_free wait", "conv: wait stg_full", "conv: wait x_empty", "conv: convert"]
-for mode, dbg in (("bf16x2", 0), ("bf16x2", 0), ("bf16x2", 2)):
+for mode, dbg in (("bf16x2", 0), ("bf16x2", 0), ("bf16x2", 2), ("bf16x2", 4), ("bf16x2", 1)):
     os.environ["FASTB200_TC_DBG"] = str(dbg)
     FM.set_head_precision(mode)
     with torch.no_grad():
