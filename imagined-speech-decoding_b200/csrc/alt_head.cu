@@ -11,9 +11,10 @@
 // floor), followed by one of three finals: temporal mean, temporal mean + Linear, flatten + Linear.  The host folds every
 // BatchNorm into (scale, shift), moves the EEGNet spatial mix in front of the temporal conv (both linear; BN1 becomes part
 // of the affine) and collapses the paper head's cnn1_t . cnn1_s into one conv -- see fast/models/alt_fused.py -- and passes
-// the chain as a fastb200_alt_head descriptor.  One CTA per (trial, window, zone) item: the window is gathered from x
-// (unfold + zone gather fused, like the Conv4Layers kernels), stages ping-pong between two shared-memory buffers, weights
-// are read through the read-only path (all threads of a warp read the same weight: threads run along time).
+// the chain as a fastb200_alt_head descriptor.  Persistent CTAs, each serving one zone: the zone's stage weights (output
+// channel fastest) and affines stay in shared memory, the window of a (trial, window) pair is gathered from x (unfold + zone
+// gather fused, like the Conv4Layers kernels) with the first stage's zero halo, stages ping-pong between two shared-memory
+// buffers, and a thread accumulates 8 consecutive conv positions of one channel in a register window.
 // These heads cost ~0.3 MFLOP per item, so this is CUDA-core code; training mode (batch statistics) stays on stock ops.
 #include "common.cuh"
 
