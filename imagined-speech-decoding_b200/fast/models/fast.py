@@ -436,7 +436,8 @@ class Conv4Layers(nn.Module):
 
 
 class CVBlock(nn.Module):
-    """EEGNet-style zone encoder with a flatten + Linear projector (reference fast.py:32-100).  Stock PyTorch ops."""
+    """EEGNet-style zone encoder with a flatten + Linear projector (reference fast.py:32-100).  Stock PyTorch ops in training mode / under
+    autograd; inside a ``Head`` in eval mode the fused kernel of ``alt_fused`` runs instead."""
 
     def __init__(self, n_channels, dim_token, dropout=0.5):
         super().__init__()
@@ -478,7 +479,8 @@ class CVBlock(nn.Module):
 
 
 class EEGNet_Encoder(nn.Module):
-    """EEGNet zone encoder with global average pooling (reference fast.py:122-167).  Stock PyTorch ops."""
+    """EEGNet zone encoder with global average pooling (reference fast.py:122-167).  Stock PyTorch ops in training mode /
+    under autograd; inside a ``Head`` in eval mode the fused kernel of ``alt_fused`` runs instead."""
 
     def __init__(self, in_channels, feature_dim, kernel_length=64, dropout=0.25):
         super().__init__()
