@@ -66,6 +66,7 @@ struct Args {
     uint32_t desc_hi, lbo16;                   // descriptor high word / LBO in 16-byte units
     int goff[FASTB200_MAX_ZONES][3];           // float offset of the packed cnn3 / cnn4 / collapsed-embed gradient block of zone z
     uint8_t cta_zone[NUM_SMS], cta_layer[NUM_SMS], cta_rank[NUM_SMS], cta_n[NUM_SMS];
+    int dbg;                                   // developer builds: bit 0 no operand loads, bit 1 no MMAs, bit 2 no embed CTAs, bit 3 no conv CTAs (pipeline probes; wrong results)
 };
 
 // =====================================================================================================================
@@ -115,7 +116,7 @@ __global__ void __launch_bounds__(THREADS_I, 1) head_wgrad_img_kernel(const __gr
     const bool emb = layer == 2;
     const int Cz = a.cz[z];
     const int rank = a.cta_rank[blockIdx.x], nc = a.cta_n[blockIdx.x];
-    const int n_it = rank < a.BN ? (a.BN - rank + nc - 1) / nc : 0;
+    const int n_it = ((a.dbg & 4) && emb) || ((a.dbg & 8) && !emb) ? 0 : rank < a.BN ? (a.BN - rank + nc - 1) / nc : 0;   // dbg bits 2 / 3: skip a layer kind
     const size_t item_sz = (size_t)F * a.TS;                        // floats per stage slot
     const uint32_t plane_bytes = (uint32_t)a.T_out * 16u;           // one plane of an image
 
@@ -151,7 +152,9 @@ __global__ void __launch_bounds__(THREADS_I, 1) head_wgrad_img_kernel(const __gr
                     uint8_t* A1 = tiles + buf * BUF_I;
                     uint8_t* Bt = A1 + (NTILE - 1) * TILE_I;
                     const uint8_t* srcB = reinterpret_cast<const uint8_t*>(a.dys + item * 3 * item_sz + (size_t)(emb ? 2 : 1 - layer) * item_sz);
-                    if (emb) {
+                    if (a.dbg & 1) {
+                        if (emb) mbar_arrive(&sm.bfull[buf]); else mbar_arrive(&sm.full[buf]);
+                    } else if (emb) {
                         mbar_expect_tx(&sm.bfull[buf], 8 * plane_bytes);
                         for (int p = 0; p < 8; ++p) bulk_g2s(Bt + p * PLANE_I, srcB + (size_t)p * plane_bytes, plane_bytes, &sm.bfull[buf]);
                     } else {
@@ -180,7 +183,7 @@ __global__ void __launch_bounds__(THREADS_I, 1) head_wgrad_img_kernel(const __gr
                 for (int j = 0; j < a.ksteps; ++j) {
                     const uint32_t acc = (it > 0 || j > 0) ? 1u : 0u;
 #pragma unroll
-                    for (int k = 0; k < NACC; ++k) umma_mn(tmem + k * NCOL, ad + 16 * j + (TWO_TAP ? 2 : 1) * k, bd + 16 * j, acc, DESC_HI_I);
+                    for (int k = 0; k < NACC; ++k) if (!(a.dbg & 2)) umma_mn(tmem + k * NCOL, ad + 16 * j + (TWO_TAP ? 2 : 1) * k, bd + 16 * j, acc, DESC_HI_I);
                 }
                 umma_commit(&sm.empty[buf]);
             }
@@ -193,7 +196,7 @@ __global__ void __launch_bounds__(THREADS_I, 1) head_wgrad_img_kernel(const __gr
                 float bs[F];
 #pragma unroll
                 for (int c = 0; c < F; ++c) bs[c] = 0.f;
-                float cur[16], nxt[16];
+                float cur[16], nxt[16], nx2[16];                     // this item's samples and the next two items' (in flight)
                 auto load = [&](int it, float (&v)[16]) {            // unfold + zone gather: sample ct of the window, every electrode of the zone
                     const int bn = rank + it * nc;
                     const int b = bn / a.n_win, n = bn - b * a.n_win;
@@ -202,10 +205,13 @@ __global__ void __launch_bounds__(THREADS_I, 1) head_wgrad_img_kernel(const __gr
                     for (int c = 0; c < 16; ++c) v[c] = (c < Cz && ct < a.W) ? __ldg(xb + (size_t)chan[c < Cz ? c : 0] * a.T) : 0.f;
                 };
                 load(0, cur);
+                if (n_it > 1) load(1, nxt);
 #pragma unroll 1
                 for (int it = 0; it < n_it; ++it) {
                     const int buf = it % NBUF, use = it / NBUF;
-                    if (it + 1 < n_it) load(it + 1, nxt);            // in flight while this item is converted
+                    // two items ahead: one iteration is shorter than a DRAM round trip under load (with a prefetch distance of one
+                    // item the embed CTAs ran at the load latency and were the kernel's long pole; three items buy nothing more)
+                    if (it + 2 < n_it) load(it + 2, nx2);
                     if (use >= 1) {
                         if (warp == 2) mbar_wait(&sm.empty[buf], (use - 1) & 1);
                         asm volatile("bar.sync 2, %0;" ::"n"(CONV_T) : "memory");
@@ -246,10 +252,8 @@ __global__ void __launch_bounds__(THREADS_I, 1) head_wgrad_img_kernel(const __gr
                     }
                     fence_proxy_async();
                     mbar_arrive(&sm.full[buf]);
-                    if (it + 1 < n_it) {
 #pragma unroll
-                        for (int c = 0; c < 16; ++c) cur[c] = nxt[c];
-                    }
+                    for (int c = 0; c < 16; ++c) { cur[c] = nxt[c]; nxt[c] = nx2[c]; }
                 }
 #pragma unroll
                 for (int c = 0; c < F; ++c) {
@@ -340,6 +344,10 @@ extern "C" int fastb200_head_bwd_tc(const fastb200_model* m, const float* packed
     a.ksteps = ceil_div(a.T_out, 16);
     a.n_win = n_win; a.step = step; a.C = m->n_chan; a.T = T; a.W = m->window_len;
     a.desc_hi = wg::im::DESC_HI_I; a.lbo16 = 128u >> 4;
+    a.dbg = 0;
+#ifdef FASTB200_DEBUG
+    if (const char* e = getenv("FASTB200_WG_DBG")) a.dbg = atoi(e);                                        // developer builds: pipeline probes
+#endif
     int n_sel = 0;
     for (int z = 0; z < m->n_zones; ++z) {
         const PackedZone p = packed_zone(*m, z);
