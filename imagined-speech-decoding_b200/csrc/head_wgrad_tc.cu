@@ -114,6 +114,11 @@ __global__ void __launch_bounds__(THREADS_I, 1) head_wgrad_img_kernel(const __gr
     const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
     const int z = a.cta_zone[blockIdx.x], layer = a.cta_layer[blockIdx.x];
     const bool emb = layer == 2;
+    // Embed layer, zones of <= 15 electrodes: electrode slot 15 of the A tile carries the constant 1, so row 15 of the tap-0
+    // accumulator IS sum_t dL/dy2 -- the collapsed-bias gradient comes out of the MMAs the layer issues anyway (1.0 is exact in
+    // bf16) and the converter warps no longer read the landed dY2 planes to sum them (40 % of their instructions: the embed CTAs
+    // were converter-bound and the kernel's long pole).
+    const bool ones = emb && a.cz[z] <= 15;
     const int Cz = a.cz[z];
     const int rank = a.cta_rank[blockIdx.x], nc = a.cta_n[blockIdx.x];
     const int n_it = ((a.dbg & 4) && emb) || ((a.dbg & 8) && !emb) ? 0 : rank < a.BN ? (a.BN - rank + nc - 1) / nc : 0;   // dbg bits 2 / 3: skip a layer kind
@@ -203,6 +208,7 @@ __global__ void __launch_bounds__(THREADS_I, 1) head_wgrad_img_kernel(const __gr
                     const float* xb = a.x + (size_t)b * a.C * a.T + (size_t)n * a.step + ct;
 #pragma unroll
                     for (int c = 0; c < 16; ++c) v[c] = (c < Cz && ct < a.W) ? __ldg(xb + (size_t)chan[c < Cz ? c : 0] * a.T) : 0.f;
+                    if (ones) v[15] = ct < a.W ? 1.0f : 0.f;
                 };
                 load(0, cur);
                 if (n_it > 1) load(1, nxt);
@@ -235,6 +241,7 @@ __global__ void __launch_bounds__(THREADS_I, 1) head_wgrad_img_kernel(const __gr
                     }
                     // sum_t dL/dy2: this thread's time sample of all 32 channels, both bf16 terms, from the landed B planes -- BEFORE the
                     // arrival below, so that the MMA (and with it the producer's refill of this buffer) cannot overtake the reads
+                    if (!ones) {
                     if (warp == 2) mbar_wait(&sm.bfull[buf], use & 1);
                     asm volatile("bar.sync 2, %0;" ::"n"(CONV_T) : "memory");
                     if (ct < a.T_out) {
@@ -250,18 +257,21 @@ __global__ void __launch_bounds__(THREADS_I, 1) head_wgrad_img_kernel(const __gr
                             }
                         }
                     }
+                    }
                     fence_proxy_async();
                     mbar_arrive(&sm.full[buf]);
 #pragma unroll
                     for (int c = 0; c < 16; ++c) { cur[c] = nxt[c]; nxt[c] = nx2[c]; }
                 }
+                if (!ones) {
 #pragma unroll
-                for (int c = 0; c < F; ++c) {
-                    const float r = warp_sum(bs[c]);
-                    if (lane == 0) atomicAdd(&sm.bsum[c], r);
+                    for (int c = 0; c < F; ++c) {
+                        const float r = warp_sum(bs[c]);
+                        if (lane == 0) atomicAdd(&sm.bsum[c], r);
+                    }
+                    asm volatile("bar.sync 1, %0;" ::"n"(CONV_T) : "memory");
+                    if (ct < F) atomicAdd(a.gpacked + a.boff[z] + ct, sm.bsum[ct]);
                 }
-                asm volatile("bar.sync 1, %0;" ::"n"(CONV_T) : "memory");
-                if (ct < F) atomicAdd(a.gpacked + a.boff[z] + ct, sm.bsum[ct]);
             }
             // ---------------- drain by warps 4-7 = TMEM lane quadrants 0-3 (a warp may only read lanes 32 (warp % 4) .. + 31):
             // TWO_TAP: quadrant 0 / 1 = a0 / a1 rows of the even tap of a pair, 2 / 3 of the odd tap; else quadrants 0 / 1 only.
@@ -285,6 +295,10 @@ __global__ void __launch_bounds__(THREADS_I, 1) head_wgrad_img_kernel(const __gr
                     if (ok && k < TAPS) {
 #pragma unroll
                         for (int co = 0; co < 32; ++co) atomicAdd(g + (row * TAPS + k) * F + co, v0[co] + v1[co]);
+                    }
+                    if (ones && q4 == 0 && kk == 0 && lane == 15) {  // the ones row (a0 part; its a1 part is 0): collapsed-bias gradient
+#pragma unroll
+                        for (int co = 0; co < 32; ++co) atomicAdd(a.gpacked + a.boff[z] + co, v0[co] + v1[co]);
                     }
                 }
             }

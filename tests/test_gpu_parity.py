@@ -619,6 +619,32 @@ def test_tc_head_zone_sizes_and_fallback(head_precision):
         assert rel_err(f, _oracle_feat64(m, cfg, x)) < TC_TOL["bf16x3"]
 
 
+def test_head_bwd_tc_zone_sizes_and_both_bias_gradient_paths(head_backward, head_precision):
+    """Tensor-core backward against the CUDA-core backward for zones of 1, 8, 9, 15 and 16 electrodes: zones of <= 15 take the
+    collapsed-bias gradient out of the MMAs (a constant-1 electrode slot in the A tile), a 16-electrode zone has no free slot
+    and sums the landed dL/dy2 planes in the converter warps."""
+    from fast.models import FAST
+    names = [f"E{i}" for i in range(49)]
+    zones = {"one": names[:1], "eight": names[1:9], "nine": names[9:18], "fifteen": names[18:33], "sixteen": names[33:49]}
+    cfg = make_small_cfg(electrodes=names, zone_dict=zones, dim_cnn=32, dim_token=32, seq_len=500, window_len=250, slide_step=125,
+                         head="Conv4Layers", n_classes=4, num_layers=1, num_heads=4, dropout=0.0)
+    torch.manual_seed(12)
+    m = FAST(cfg).cuda().train()
+    g = torch.Generator().manual_seed(6)
+    x = (torch.randn(9, 49, 500, generator=g) * 3.0).cuda()
+    y = torch.randint(0, 4, (9,), generator=g).cuda()
+    grads = {}
+    for bwd in ("ffma", "tc"):
+        head_backward(bwd)
+        head_precision("fp32" if bwd == "ffma" else "bf16x2")
+        m.zero_grad(set_to_none=True)
+        torch.nn.CrossEntropyLoss()(m(x), y).backward()
+        grads[bwd] = {k: p.grad.clone() for k, p in m.named_parameters()}
+    for k in grads["ffma"]:
+        e = rel_err(grads["tc"][k], grads["ffma"][k])
+        assert e < TOL, (k, e)
+
+
 def test_head_bwd_tc_weight_gradients_vs_ffma_at_scale(head_backward, head_precision):
     """cnn3 / cnn4 weight gradients from the tcgen05 kernel against the CUDA-core kernel on a batch large enough that every
     persistent CTA walks many items (TMEM accumulation across items, staging ring and tile double-buffer wrap-around)."""
