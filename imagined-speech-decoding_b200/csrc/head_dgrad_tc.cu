@@ -75,7 +75,7 @@ struct Smem {
     uint64_t w_full;
     uint64_t stg_full[2][2], stg_empty[2][2];
     uint64_t ya_ready[2][2], tile_free[2][2];  // per stream, per item parity
-    uint64_t yb_ready[2], dm_full[2], d_free[2];
+    uint64_t yb_ready[2], dm_full[2][2], d_free[2];    // dm_full[stream][layer]: one completion per item each
     uint32_t tmem_base;
 };
 static_assert(sizeof(Smem) <= SMEM_HDR, "Smem header overflows its reservation");
@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(THREADS, 1) head_dgrad_tc_kernel(const __grid_
     constexpr int LB = lb(NT);
     constexpr int STG = stg_tiles(NT);
     constexpr int DCOLS = 32 * NT;
-    constexpr int TMEM_COLS = 2 * DCOLS <= 128 ? 128 : 256;
+    constexpr int TMEM_COLS = 4 * DCOLS <= 256 ? 256 : 512;         // per stream one accumulator PER LAYER: columns (2 layer + s) DCOLS
 
     const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
     const int z = a.cta_zone[blockIdx.x];
@@ -107,7 +107,8 @@ __global__ void __launch_bounds__(THREADS, 1) head_dgrad_tc_kernel(const __grid_
                 mbar_init(&sm.tile_free[s][i], 1);
             }
             mbar_init(&sm.yb_ready[s], EPI_WARPS * 16);
-            mbar_init(&sm.dm_full[s], 1);
+            mbar_init(&sm.dm_full[s][0], 1);
+            mbar_init(&sm.dm_full[s][1], 1);
             mbar_init(&sm.d_free[s], EPI_WARPS * 16);
         }
         fence_mbar_init();
@@ -144,13 +145,15 @@ __global__ void __launch_bounds__(THREADS, 1) head_dgrad_tc_kernel(const __grid_
         const uint32_t w_c4 = smem_u32(wz), w_c3 = w_c4 + CONV_CHUNKS * LB;
         auto issue_conv = [&](int layer, int it) {           // layer 0: cnn4^T on dL/dy4, layer 1: cnn3^T on dL/dy3
             if (layer == 0) {
+                // its accumulator was drained by the dL/dy3 epilogue of item it - 1, which the issuer has already waited for
+                // (yb_ready in front of layer 1 of item it - 1)
                 mbar_wait(&sm.ya_ready[s][it & 1], (it >> 1) & 1);
-                if (it > 0) mbar_wait(&sm.d_free[s], (it - 1) & 1);
             } else {
                 mbar_wait(&sm.yb_ready[s], it & 1);
+                if (it > 0) mbar_wait(&sm.d_free[s], (it - 1) & 1);  // the dL/dy2 epilogue of item it - 1 drained this layer's accumulator
             }
             tc_fence_after();
-            const uint32_t d = tmem + s * DCOLS;
+            const uint32_t d = tmem + (2 * layer + s) * DCOLS;
             const uint32_t yd = desc_lo(smem_u32(ys) + (2 * s + (it & 1)) * y_bytes(NT), RY * 16);
             const uint32_t wd = desc_lo(layer == 0 ? w_c4 : w_c3, LB);
             uint32_t acc = 0;
@@ -164,12 +167,16 @@ __global__ void __launch_bounds__(THREADS, 1) head_dgrad_tc_kernel(const __grid_
                              idesc_bf16(32 * (NT - t)), acc);
                         acc = 1;
                     }
-            umma_commit(&sm.dm_full[s]);
+            umma_commit(&sm.dm_full[s][layer]);
             if (layer == 1) umma_commit(&sm.tile_free[s][it & 1]);       // the operand tile of this parity may be rewritten
         };
+        // Software pipeline across items: cnn3^T of item it and cnn4^T of item it + 1 are issued back to back (separate
+        // accumulators), so the tensor pipe has 40 MMAs of this stream queued while the epilogue warps turn dL/dy2(it) and then
+        // dL/dy3(it + 1) around -- with one accumulator the chain cnn4^T -> epilogue -> cnn3^T -> drain was strictly serial per item.
+        issue_conv(0, 0);
         for (int it = 0; it < n_it; ++it) {
-            issue_conv(0, it);
             issue_conv(1, it);
+            if (it + 1 < n_it) issue_conv(0, it + 1);
         }
     } else if (warp >= COPY_WARP0 && warp < CONV_WARP0) {
         // ============================ copier of stream s: saved y4 rows + dfeat row -> staging ring ============================
@@ -265,11 +272,12 @@ __global__ void __launch_bounds__(THREADS, 1) head_dgrad_tc_kernel(const __grid_
             mbar_wait(bar, parity);
 #endif
         };
-        auto drain = [&](float (&v)[CW]) {
+        auto drain = [&](int layer, float (&v)[CW]) {
             float u[NT - 1][CW];
-            tmem_ld16(lane_addr, v);
+            const uint32_t addr = lane_addr + layer * (2 * 32 * NT);
+            tmem_ld16(addr, v);
 #pragma unroll
-            for (int tm = 1; tm < NT; ++tm) tmem_ld16(lane_addr + 32 * tm, u[tm - 1]);
+            for (int tm = 1; tm < NT; ++tm) tmem_ld16(addr + 32 * tm, u[tm - 1]);
             tmem_ld_wait();
 #pragma unroll
             for (int tm = 1; tm < NT; ++tm)
@@ -292,10 +300,10 @@ __global__ void __launch_bounds__(THREADS, 1) head_dgrad_tc_kernel(const __grid_
 #pragma unroll 1
         for (int it = 0; it < n_it; ++it) {
             // ---- dL/dy3: drain -> masked -> operand tile of this parity (overwrites dL/dy4, already consumed) + global
-            group_wait(&sm.dm_full[s], 0);
+            group_wait(&sm.dm_full[s][0], it & 1);
             tc_fence_after();
             float v[CW];
-            drain(v);
+            drain(0, v);
             {
                 uint8_t* yt = yt0 + (it & 1) * y_bytes(NT);
 #pragma unroll
@@ -314,9 +322,9 @@ __global__ void __launch_bounds__(THREADS, 1) head_dgrad_tc_kernel(const __grid_
                 mbar_arrive(&sm.yb_ready[s]);
             }
             // ---- dL/dy2: drain -> global
-            group_wait(&sm.dm_full[s], 1);
+            group_wait(&sm.dm_full[s][1], it & 1);
             tc_fence_after();
-            drain(v);
+            drain(1, v);
             tc_fence_before();
             mbar_arrive(&sm.d_free[s]);
 #pragma unroll
