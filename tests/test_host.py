@@ -164,3 +164,52 @@ def test_filter_design_helpers(filter_golden):
     np.testing.assert_allclose(F._kaiser_lowpass(4, 5), filter_golden["h_4_5"], rtol=1e-10, atol=1e-14)
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         F.sosfiltfilt(filter_golden["sos"], torch.zeros(2, 100))
+
+
+def test_alternative_head_chain_folding_matches_the_modules_on_cpu():
+    """Host logic of the fused eval-mode alternative heads (fast/models/alt_fused.py): the stage chain handed to
+    fastb200_alt_head_fwd -- BatchNorm folded into (scale, shift), EEGNet's spatial mix moved in front of the temporal filter,
+    the paper head's cnn1_t . cnn1_s collapsed, weights laid out output-channel-fastest -- evaluated with plain torch ops in
+    fp64 equals the module in eval mode (no kernel involved)."""
+    import torch.nn.functional as F
+    from fast.models import CVBlock, EEGNet_Encoder, HeadConv_Paper_Version
+    from fast.models import alt_fused as A
+
+    def run_chain(enc, x):
+        stages, final = A._chain(enc)
+        y = x
+        for st in stages:
+            in_ch = y.shape[1]
+            if st["kind"] == A.DENSE:
+                w = st["w"].reshape(in_ch, st["k"], st["out_ch"]).permute(2, 0, 1)
+                y = F.conv1d(y, w, padding=st["pad"])
+            else:
+                w = st["w"].reshape(st["k"], st["out_ch"]).t().reshape(st["out_ch"], 1, st["k"])
+                y = F.conv1d(y, w, padding=st["pad"], groups=in_ch)
+            if "scale" in st:
+                y = y * st["scale"][None, :, None] + st["shift"][None, :, None]
+            y = F.elu(y) if st["act"] == A.ACT_ELU else F.gelu(y) if st["act"] == A.ACT_GELU else y
+            if st["pool_kind"] == A.POOL_AVG:
+                y = F.avg_pool1d(y, st["pool"])
+            elif st["pool_kind"] == A.POOL_MAX:
+                y = F.max_pool1d(y, st["pool"])
+        if final["kind"] == A.FINAL_MEAN:
+            return y.mean(-1)
+        y = y.mean(-1) if final["kind"] == A.FINAL_MEAN_LINEAR else y.flatten(1)
+        return y @ final["w"].reshape(final["lin_out"], final["lin_in"]).t() + final["b"]
+
+    g = torch.Generator().manual_seed(5)
+    for cls, args in ((CVBlock, (6, 32)), (EEGNet_Encoder, (6, 32)), (HeadConv_Paper_Version, (6, 32)), (EEGNet_Encoder, (4, 16, 32))):
+        torch.manual_seed(1)
+        enc = cls(*args).double()
+        for mod in enc.modules():
+            if isinstance(mod, torch.nn.BatchNorm2d):
+                mod.running_mean.copy_(torch.randn(mod.num_features, generator=g).double())
+                mod.running_var.copy_(torch.rand(mod.num_features, generator=g).double() + 0.5)
+                mod.weight.data.copy_(torch.randn(mod.num_features, generator=g).double())
+                mod.bias.data.copy_(torch.randn(mod.num_features, generator=g).double())
+        enc.eval()
+        x = torch.randn(5, args[0], 250, generator=g).double()
+        with torch.no_grad():
+            ref, got = enc(x), run_chain(enc, x)
+        assert float((ref - got).abs().max() / ref.abs().max()) < 1e-12, cls.__name__
