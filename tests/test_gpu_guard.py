@@ -167,3 +167,37 @@ def test_filter_kernels_stay_inside_their_buffers(rows, T):
     torch.cuda.synchronize()
     x.check("filter input after the fused kernel")
     assert out.shape == (rows, -(-T * 4 // 5)) and torch.equal(out, chain)
+
+
+@pytest.mark.parametrize("head", ["CVBlock", "EEGNet_Encoder", "HeadConv_Paper_Version"])
+def test_alternative_head_kernel_stays_inside_its_output(head):
+    """fastb200_alt_head_fwd through the C ABI: every feature written, nothing outside the buffer (ragged batch, step override),
+    and the descriptor checks reject a window length the flatten + Linear head cannot take."""
+    from fast import _native as N
+    from fast.models import FAST
+    torch.manual_seed(1)
+    m = FAST(make_prod_cfg(head=head, dropout=0.0)).cuda().eval()
+    runner = m.head._alt_runner()
+    B, T, step = 7, 800, 50
+    x = Guarded(B * 64 * T)
+    x.t.copy_(torch.randn(B * 64 * T, device="cuda"))
+    with torch.no_grad():
+        ref = m.forward_head(x.t.view(B, 64, T), step)                      # builds the descriptor + packed parameters
+    n_win = (T - 250) // step + 1
+    F_out = runner.desc.lin_out
+    feat = Guarded(B * n_win * 8 * F_out)
+    N.check(N.lib().fastb200_alt_head_fwd(runner.desc, N.ptr(runner.packed), N.ptr(x.t), B, 64, T, n_win, step, N.ptr(feat.t),
+                                          N.stream_ptr()), "alt_head_fwd")
+    torch.cuda.synchronize()
+    feat.check("alt_head_fwd feat", fully_written=True)
+    x.check("x")
+    assert torch.equal(feat.t.view_as(ref), ref)
+    lib = N.lib()
+    assert lib.fastb200_alt_head_fwd(runner.desc, N.ptr(runner.packed), N.ptr(x.t), B, 64, 300, 3, 125, N.ptr(feat.t), N.stream_ptr()) < 0
+    assert b"windows run past" in lib.fastb200_last_error()
+    if head == "CVBlock":                                                   # flatten + Linear(256): only 250-sample windows fit
+        import copy
+        d2 = copy.copy(runner.desc)
+        d2.window_len = 200
+        assert lib.fastb200_alt_head_fwd(d2, N.ptr(runner.packed), N.ptr(x.t), B, 64, T, 2, 125, N.ptr(feat.t), N.stream_ptr()) < 0
+        assert b"flatten+linear" in lib.fastb200_last_error()
