@@ -79,6 +79,7 @@ class FusedTrainer:
         # mask of parameters the chosen mode does not train: their gradient stays zero, but AdamW's weight decay
         # would still move them -- the reference never hands them a .grad, so torch's AdamW skips them.
         self._frozen = None
+        self._host_stage = None    # double-buffered device staging of host batches (_stage_host)
         if self.freeze_head or self.mode == N.MODE_TRAIN_HEAD:
             keep = torch.zeros(n, device=dev, dtype=torch.bool)
             for name, _, off, cnt in model._fp.items:
@@ -239,18 +240,49 @@ class FusedTrainer:
             return [(lambda: self._launch_eval(ws), True)]
         return [(lambda: self._launch_train(ws), True)]
 
+    def _stage_host(self, x, y):
+        """Host batch -> one of two device staging pairs on a SIDE stream; the caller's stream waits for the copy only.  A call
+        returns as soon as its work is enqueued, so the copy of batch k + 1 (issued by the next call) runs beside the kernels
+        of batch k: end to end the step costs max(copy, kernels) instead of their sum (pin the host tensors for that)."""
+        key = (tuple(x.shape), y.dtype)
+        st = self._host_stage
+        if st is None or st["key"] != key:
+            st = dict(key=key, k=0, x=[torch.empty(x.shape, device=self.device) for _ in range(2)],
+                      y=[torch.empty(y.shape, dtype=y.dtype, device=self.device) for _ in range(2)],
+                      copied=[torch.cuda.Event() for _ in range(2)], freed=[torch.cuda.Event() for _ in range(2)],
+                      stream=torch.cuda.Stream(self.device))
+            st["stream"].wait_stream(torch.cuda.current_stream(self.device))
+            self._host_stage = st
+        b = st["k"] & 1
+        side = st["stream"]
+        with torch.cuda.stream(side):
+            if st["k"] >= 2:
+                side.wait_event(st["freed"][b])
+            st["x"][b].copy_(x, non_blocking=True)
+            st["y"][b].copy_(y, non_blocking=True)
+            st["copied"][b].record(side)
+        torch.cuda.current_stream(self.device).wait_event(st["copied"][b])
+        st["k"] += 1
+        return st["x"][b], st["y"][b], st["freed"][b]
+
     def _run(self, x, y, train):
-        N.require_cuda(x, "x")
         if x.dtype != torch.float32:
             x = x.float()
         if y.dtype not in (torch.uint8, torch.int64):
             y = y.long()
         self._rebind_if_moved()
+        freed = None
+        if not x.is_cuda:                                    # host batch (pinned for full speed): staged on a side stream
+            with torch.cuda.device(self.device):
+                x, y, freed = self._stage_host(x, y.cpu() if y.is_cuda else y)
+        N.require_cuda(x, "x")
         ws = self._workspace(x.shape[0], x.shape[2], y.dtype, train)
         phases = self._phases(ws, train)
         with torch.cuda.device(self.device):
             ws["x"].copy_(x, non_blocking=True)
             ws["y"].copy_(y.to(self.device, non_blocking=True), non_blocking=True)
+            if freed is not None:
+                freed.record(torch.cuda.current_stream(self.device))
             if not self.use_graph:
                 for fn, _ in phases:
                     fn()
@@ -287,7 +319,8 @@ class FusedTrainer:
 
     # ------------------------------------------------------------------------------------------ public API
     def train_step(self, x, y):
-        """One optimiser step on batch (x (B,C,T) float32 CUDA, y (B,) uint8/int64).  Returns (loss, n_correct):
+        """One optimiser step on batch (x (B,C,T) float32, y (B,) uint8/int64; CUDA tensors, or HOST tensors -- pinned for full
+        speed -- which are uploaded on a side stream so that the next call's copy overlaps this call's kernels).  Returns (loss, n_correct):
         1-element device tensors that the NEXT call overwrites -- read them (``.item()``) only when needed."""
         if self.lr_by_step and self.steps_done >= self.n_sched:
             raise RuntimeError(f"LR schedule has {self.n_sched} entries; step {self.steps_done + 1} is past its end")

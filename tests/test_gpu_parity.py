@@ -450,6 +450,29 @@ def test_fused_trainer_matches_oracle_loop(use_graph):
     assert int(n_correct) == int((pred.cpu() == batches[0][1].long()).sum())
 
 
+def test_fused_trainer_host_batches_equal_device_batches():
+    """train_step / eval_step fed pinned HOST batches (uploaded on the trainer's side stream through two staging pairs, so that
+    consecutive steps overlap copy and kernels) follow the same loss trajectory as the same batches given as CUDA tensors."""
+    from fast.train import FusedTrainer
+    g = torch.Generator().manual_seed(21)
+    batches = [(torch.randn(8, 64, 795, generator=g) * 3, torch.randint(0, 5, (8,), generator=g).to(torch.uint8)) for _ in range(5)]
+    out = {}
+    for where in ("cuda", "host"):
+        m = _prod_model(dropout=0.0).train()
+        ft = FusedTrainer(m, lr=5e-4, use_graph=True)
+        losses = []
+        for x, y in batches:
+            xb, yb = (x.cuda(), y.cuda()) if where == "cuda" else (x.pin_memory(), y.pin_memory())
+            loss, _ = ft.train_step(xb, yb)
+            losses.append(loss.clone())                             # read later: the calls stay asynchronous
+        x, y = batches[0]
+        l, nc, pred = ft.eval_step(*((x.cuda(), y.cuda()) if where == "cuda" else (x.pin_memory(), y.pin_memory())))
+        out[where] = ([float(v) for v in losses], float(l), int(nc), pred.cpu())
+    np.testing.assert_allclose(out["host"][0], out["cuda"][0], rtol=2e-5, atol=2e-6)
+    assert abs(out["host"][1] - out["cuda"][1]) < 2e-5 and out["host"][2] == out["cuda"][2]
+    assert torch.equal(out["host"][3], out["cuda"][3])
+
+
 def test_dropout_train_mode_is_consistent():
     """p = 0.1: masks are regenerated identically in the backward (directional derivative check through the C ABI) and
     change between steps; eval mode ignores them."""
