@@ -473,14 +473,16 @@ def test_fused_trainer_host_batches_equal_device_batches():
     assert torch.equal(out["host"][3], out["cuda"][3])
 
 
-def test_dropout_train_mode_is_consistent():
-    """p = 0.1: masks are regenerated identically in the backward (directional derivative check through the C ABI) and
-    change between steps; eval mode ignores them."""
+@pytest.mark.parametrize("B", [6, 700])
+def test_dropout_train_mode_is_consistent(B):
+    """p = 0.1: masks are regenerated identically in the backward (directional derivative check through the C ABI; batch 6 runs
+    the six-warps-per-trial schedule of the token kernels, batch 700 the warp-per-trial one) and change between steps; eval
+    mode ignores them."""
     from fast import _native as N
     m = _prod_model(dropout=0.1).train()
     flat, desc = m._runtime()
     lib = N.lib()
-    B, n_win = 6, 5
+    n_win = 5
     gen = torch.Generator(device='cuda').manual_seed(2)
     feat = torch.randn(B, n_win, 8, 32, device='cuda', generator=gen)
     logits = torch.empty(B, 5, device='cuda'); saved = torch.empty(lib.fastb200_transformer_saved_floats(desc, B, n_win), device='cuda')
@@ -493,7 +495,7 @@ def test_dropout_train_mode_is_consistent():
     assert torch.equal(logits, l2)                                         # same (seed, offset) -> same masks
     fwd(flat, 5, 10, l2)
     assert not torch.equal(logits, l2)                                     # new offset -> new masks
-    w = torch.randn(B, 5, device='cuda', generator=gen)                    # L = sum(w * logits)
+    w = torch.randn(B, 5, device='cuda', generator=gen) * (6.0 / B)        # L = sum(w * logits)
     grads = torch.zeros_like(flat); dfeat = torch.empty_like(feat)
     N.check(lib.fastb200_transformer_bwd(desc, N.ptr(flat), N.ptr(feat), N.ptr(saved), N.ptr(w), B, n_win, 0, 0.1, 5, 9, None,
                                          N.ptr(grads), N.ptr(dfeat), N.stream_ptr()), "tbwd")
