@@ -127,3 +127,37 @@ def test_fused_filter_support_predicate_is_host_logic(libpath):
     assert sup(795, 4, 27, 636, h61, 4, 5, npr61) == 1       # same alignment as the default, fewer taps
     rc = lib.fastb200_sosfiltfilt_resample(None, 4, None, 4, 0, 795, None, 4, 27, 636, None, 106, 4, 5, 11, None)
     assert rc < 0 and b"NULL" in lib.fastb200_last_error()
+
+
+def test_alt_head_descriptor_validation_without_a_gpu(libpath):
+    """fastb200_alt_head_fwd rejects malformed chains before any launch (messages through fastb200_last_error)."""
+    from fast import _native as N
+    lib = N.lib()
+    assert lib.fastb200_sizeof_alt_head() == ctypes.sizeof(N.AltHeadDesc)
+    d = N.AltHeadDesc()
+    assert lib.fastb200_alt_head_fwd(None, None, None, 1, 8, 500, 1, 125, None, None) < 0
+    d.window_len, d.n_zones, d.n_stages = 250, 1, 1
+    d.zone_size[0], d.zone_off[0] = 4, 0
+    st = d.stage[0]
+    st.kind, st.out_ch, st.k, st.pad, st.act, st.pool_kind, st.pool, st.scale_off = 1, 8, 3, 0, 0, 0, 1, -1      # depth-wise first stage
+    assert lib.fastb200_alt_head_fwd(d, None, None, 1, 8, 500, 1, 125, None, None) < 0
+    assert b"must be dense" in lib.fastb200_last_error()
+    st.kind, st.pool_kind, st.pool = 0, 1, 3                                                                       # pool size not instantiated
+    assert lib.fastb200_alt_head_fwd(d, None, None, 1, 8, 500, 1, 125, None, None) < 0
+    assert b"pool size 3" in lib.fastb200_last_error()
+    st.pool = 2
+    d.final_kind, d.lin_in, d.lin_out = 2, 999, 4                                                                  # flatten + Linear of the wrong width
+    assert lib.fastb200_alt_head_fwd(d, None, None, 1, 8, 500, 1, 125, None, None) < 0
+    assert b"flatten+linear" in lib.fastb200_last_error()
+    d.final_kind, d.lin_out = 0, 8
+    assert lib.fastb200_alt_head_fwd(d, None, None, 1, 8, 100, 1, 125, None, None) < 0                             # window longer than the trial
+    assert b"windows run past" in lib.fastb200_last_error()
+    assert lib.fastb200_alt_head_fwd(d, None, None, 0, 8, 500, 1, 125, None, None) == 0                            # empty batch: nothing to do
+
+
+def test_static_workspace_entry_point_validation_without_a_gpu(libpath):
+    from fast import _native as N
+    lib = N.lib()
+    assert lib.fastb200_head_bwd_tc_static_max_floats() * 4 == 32 << 20
+    assert lib.fastb200_head_bwd_tc_static(None, None, None, None, None, 1, 800, 5, 125, None, None) < 0
+    assert b"NULL" in lib.fastb200_last_error()
